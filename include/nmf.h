@@ -1,0 +1,166 @@
+/* nmf.h — C ABI of libnmf_b200.so: a B200 (sm_100a) drop-in for the update_div hot path of
+ * recoord/nmf-gpu ("nmf-cuda").  Plain pointers and sizes only; no C++/torch types.
+ *
+ * Part 1 is the reference's documented API (its README.md:31-54) — same names, argument
+ * meaning and error behaviour.  Part 2 is the session API the Python/C++ hosts, the benchmark
+ * and the multi-GPU launcher use; it exposes the same iteration with device-resident data.
+ * Part 3 are kernel-level entry points used only by the parity tests.
+ *
+ * Error behaviour (reference: cuda/error-check.hpp:9-17,55-60 and the shape checks at
+ * cuda/matrix.cu:130-134,206-210,...): a failing CUDA call or a shape mismatch prints to stderr
+ * and exit()s.  Hosts that prefer status codes call nmf_set_error_mode(1): every function of
+ * parts 2 and 3 then returns non-zero on failure and nmf_last_error() holds the message
+ * (part-1 functions are void, as in the reference; they still exit in mode 0 and set the
+ * message / return early in mode 1).
+ */
+#ifndef NMF_B200_H
+#define NMF_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------
+ * Part 1 — the reference's host API
+ * ------------------------------------------------------------------------------------------ */
+
+/* The README's "matrix struct" (README.md:31-36): a host column-major float array plus its two
+ * dims.  The struct itself is not defined in the reference tree (its code moved on to the C++
+ * class Matrix of cuda/matrix.cuh:18-39); this is the layout of the upstream nmf-cuda lineage.
+ *   mat    host, column-major, dim[0] x dim[1], leading dimension dim[0]
+ *   mat_d  optional device mirror owned by the library (NULL unless the library set it)
+ *   dim    {rows, cols}                                                                  */
+typedef struct {
+    float *mat;
+    float *mat_d;
+    int    dim[2];
+} matrix;
+
+/* Replaces `Matrix read_matrix(std::string file, cudaStream_t)`, cuda/nmf.cu:188-218.
+ * File: int32 rows, int32 cols, float32[rows*cols] column-major (README.md:33-34).
+ * Values < EPS are raised to EPS ("make sure no zero elements", nmf.cu:210-211).
+ * Prints "read <file> [<rows_padded>x<cols_padded>]" like nmf.cu:215. A->mat is malloc'ed. */
+void read_matrix(matrix *A, const char *file);
+
+/* Replaces `void write_matrix(Matrix*, std::string, cudaStream_t)`, cuda/nmf.cu:220-259.
+ * Same format, un-padded; prints "write <file> [<rows>x<cols>]" like nmf.cu:258. */
+void write_matrix(matrix A, const char *file);
+
+/* rows x cols matrix filled with `value` (reference: Matrix(float value, rows, cols, stream),
+ * cuda/matrix.cu:69-80). */
+void create_matrix(matrix *A, int rows, int cols, float value);
+
+/* Frees A->mat (and A->mat_d if set); reference: Matrix::~Matrix, cuda/matrix.cu:82-86. */
+void destroy_matrix(matrix *A);
+
+/* README.md:38-54.  Replaces run_async + update_h + update_w, cuda/nmf.cu:76-176.
+ *   W (MxK), H (KxN): initial factors, UPDATED IN PLACE (through W.mat / H.mat)
+ *   X (MxN)         : target
+ *   CONVERGE_THRESH : stop when (previous cost - cost) / cost < CONVERGE_THRESH, tested every
+ *                     25 iterations (ITER_CHECK, nmf.cu:9); 0 => always max_iter iterations
+ *   max_iter        : maximum number of iterations
+ *   t               : NULL, or >= 10 doubles receiving seconds per phase:
+ *                     t[0] W*H GEMM with the fused clamp+divide (+cost), t[1] 0 (fused into t[0]),
+ *                     t[2] row/column sums, t[3] W'Y / YH' GEMMs with the fused divide+multiply,
+ *                     t[4] 0 (fused into t[3]), t[5] W multiply/update kernel, t[6] cost read-back
+ *                     and convergence test, t[7] allreduce, t[8] H2D/D2H + allocation + setup,
+ *                     t[9] total wall time of the call
+ *   verbose         : 1 prints the cost every 25 iterations
+ * Semantics (exact | refcompat) and GPU selection come from the environment: NMF_SEMANTICS,
+ * NMF_DEVICE, NMF_ENGINE; defaults: exact, device 0, tcgen05 engine. */
+void update_div(matrix W, matrix H, matrix X, float CONVERGE_THRESH, int max_iter, double t[10],
+                int verbose);
+
+/* ------------------------------------------------------------------------------------------
+ * Part 2 — options, sessions (device-resident data), multi-GPU
+ * ------------------------------------------------------------------------------------------ */
+
+enum { NMF_EXACT = 0, NMF_REFCOMPAT = 1 };   /* SURVEY.md §0.4 */
+enum { NMF_ENGINE_TCGEN05 = 0,               /* tcgen05/TMEM/TMA 3xTF32 kernels (the product path) */
+       NMF_ENGINE_SIMT = 1 };                /* plain fp32 FFMA kernels: bring-up / debugging aid  */
+
+typedef struct {
+    int semantics;      /* NMF_EXACT | NMF_REFCOMPAT                                        */
+    int engine;         /* NMF_ENGINE_*                                                     */
+    int device;         /* CUDA device ordinal; -1 = current device                         */
+    int check_every;    /* cost / convergence period; 0 => 25 (ITER_CHECK)                  */
+    int use_graph;      /* 1: replay one CUDA graph per iteration (reference: nmf.cu:100-115) */
+    int tf32_passes;    /* 3 = 3xTF32 (fp32-equivalent, default); 1 = single-pass TF32      */
+    int reserved[10];
+} nmf_options;
+
+typedef struct {
+    int    iterations;        /* iterations executed                                          */
+    int    converged;         /* 1 if stopped by CONVERGE_THRESH                              */
+    double cost;              /* last evaluated KL divergence (NaN if never evaluated)        */
+    double device_ms;         /* cudaEvent time of the iteration loop only                    */
+    long long gpu_launches;   /* kernels of this library launched inside the loop             */
+} nmf_result;
+
+void nmf_default_options(nmf_options *o);          /* fills defaults, then applies NMF_* env    */
+int  nmf_set_error_mode(int mode);                 /* 0 exit (reference), 1 return codes        */
+const char *nmf_last_error(void);
+const char *nmf_version(void);
+
+/* update_div with explicit options and a result record. */
+int nmf_update_div_ex(matrix W, matrix H, matrix X, float CONVERGE_THRESH, int max_iter,
+                      double t[10], int verbose, const nmf_options *opt, nmf_result *res);
+
+/* A session owns the device buffers of one rank's shard: W (M x K, replicated), the local column
+ * block of H (K x n_local) and X (M x n_local).  n_offset / n_global locate the block in the
+ * full problem (needed by the refcompat column mask and the synthetic generator). */
+typedef struct nmf_session nmf_session;
+
+nmf_session *nmf_session_create(int M, int n_local, int K, long long n_offset, long long n_global,
+                                const nmf_options *opt);
+void nmf_session_destroy(nmf_session *s);
+
+/* Host (column-major, unpadded) -> device; values < EPS are clamped as read_matrix does.
+ * Any of the three may be NULL to leave that matrix unchanged. */
+int nmf_session_upload(nmf_session *s, const float *W, const float *H_local, const float *X_local);
+/* Device -> host; either may be NULL. */
+int nmf_session_download(nmf_session *s, float *W, float *H_local);
+
+/* Synthetic uniform(0,1) data generated on the device from a counter-based hash of the GLOBAL
+ * (row, col) index, so any column sharding yields the same problem.  which: bit0 W, bit1 H, bit2 X */
+int nmf_session_fill_uniform(nmf_session *s, unsigned long long seed, int which);
+
+/* Join an NCCL communicator (one process per GPU).  id = 128-byte ncclUniqueId obtained from
+ * nmf_nccl_unique_id() on rank 0 and broadcast by the host (torch.distributed, MPI, a file...). */
+int nmf_nccl_unique_id(void *id128);
+int nmf_session_join(nmf_session *s, int rank, int nranks, const void *id128);
+
+/* Runs the iteration (the body of update_div) on the resident data. */
+int nmf_session_run(nmf_session *s, float CONVERGE_THRESH, int max_iter, double t[10], int verbose,
+                    nmf_result *res);
+
+/* KL divergence of the resident factors (allreduced over ranks when joined). */
+int nmf_session_cost(nmf_session *s, double *cost);
+
+/* ------------------------------------------------------------------------------------------
+ * Part 3 — kernel-level entry points for the parity tests (host arrays, column-major)
+ * ------------------------------------------------------------------------------------------ */
+
+/* Y = X ./ max(W*H, EPS) (reference: matrix_multiply + set_epsilon + element_divide,
+ * nmf.cu:125-131); *cost (may be NULL) = KL divergence of (X, W*H). */
+int nmf_dbg_quotient(const float *W, const float *H, const float *X, float *Y, double *cost,
+                     int M, int N, int K, const nmf_options *opt);
+/* One H half-step (nmf.cu:118-146) / one W half-step (nmf.cu:148-176), in place. */
+int nmf_dbg_h_step(const float *W, float *H, const float *X, int M, int N, int K, const nmf_options *opt);
+int nmf_dbg_w_step(float *W, const float *H, const float *X, int M, int N, int K, const nmf_options *opt);
+/* Column sums of W (len K) and row sums of H (len K), clamped to >= EPS
+ * (sum_cols/sum_rows + set_epsilon, nmf.cu:134-135,164-165). */
+int nmf_dbg_sums(const float *W, const float *H, float *sumW, float *sumH, int M, int N, int K,
+                 const nmf_options *opt);
+/* Raw tensor-core contraction used by all three GEMMs, for descriptor/layout bring-up:
+ * which = 0: C(MxN) = A(MxK)*B(KxN);  1: C(KxN) = A(MxK)'*B(MxN);  2: C(MxK) = A(MxN)*B(KxN)'
+ * (shapes named as in the NMF use: A,B,C column-major).  passes = 1 or 3. */
+int nmf_dbg_gemm(int which, const float *A, const float *B, float *C, int M, int N, int K,
+                 int passes, const nmf_options *opt);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NMF_B200_H */

@@ -1,0 +1,319 @@
+// api.cpp — the extern "C" boundary of libnmf_b200.so (include/nmf.h): the reference's host API
+// (read_matrix / write_matrix / update_div, README.md:31-54) plus the session and test entry points.
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <functional>
+#include <string>
+#include <vector>
+
+#include "session.hpp"
+
+namespace nmf {
+nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, long long n_global, const nmf_options& opt);
+void session_upload(nmf_session_impl& s, const float* W, const float* H, const float* X);
+void session_download(nmf_session_impl& s, float* W, float* H);
+void session_fill_uniform(nmf_session_impl& s, unsigned long long seed, int which);
+void session_run(nmf_session_impl& s, float thresh, int max_iter, double t[10], int verbose, nmf_result* res);
+void session_cost(nmf_session_impl& s, double* cost);
+}  // namespace nmf
+
+using namespace nmf;
+
+namespace {
+
+int g_error_mode = 0;                 // 0: print + exit (reference convention), 1: return codes
+thread_local std::string g_last_error;
+
+// Runs body; on failure follows the reference's convention (cuda/error-check.hpp:9-17: print and
+// exit(code)) or, in mode 1, records the message and returns the code.
+int guarded(const std::function<void()>& body) {
+    try {
+        body();
+        return 0;
+    } catch (const Error& e) {
+        g_last_error = e.what();
+        if (g_error_mode == 0) { std::fprintf(stderr, "nmf_b200: %s\n", e.what()); std::exit(e.code); }
+        return e.code ? e.code : 1;
+    } catch (const std::exception& e) {
+        g_last_error = e.what();
+        if (g_error_mode == 0) { std::fprintf(stderr, "nmf_b200: %s\n", e.what()); std::exit(1); }
+        return 1;
+    }
+}
+
+int env_int(const char* name, int dflt) {
+    const char* v = std::getenv(name);
+    return (v && *v) ? std::atoi(v) : dflt;
+}
+
+nmf_options resolve(const nmf_options* opt) {
+    nmf_options o;
+    if (opt) o = *opt; else nmf_default_options(&o);
+    return o;
+}
+
+void check_shapes(const matrix& W, const matrix& H, const matrix& X) {
+    NMF_CHECK(W.mat && H.mat && X.mat, "update_div: NULL matrix data");
+    // the reference's wrappers exit on mismatching dims (e.g. cuda/matrix.cu:130-134)
+    NMF_CHECK(W.dim[0] == X.dim[0] && H.dim[1] == X.dim[1] && W.dim[1] == H.dim[0],
+              "update_div: dimensions do not agree (need W MxK, H KxN, X MxN)");
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* nmf_version(void) { return "nmf-b200 0.1 (sm_100a)"; }
+int nmf_set_error_mode(int mode) { const int old = g_error_mode; g_error_mode = mode ? 1 : 0; return old; }
+const char* nmf_last_error(void) { return g_last_error.c_str(); }
+
+void nmf_default_options(nmf_options* o) {
+    std::memset(o, 0, sizeof(*o));
+    o->semantics = NMF_EXACT;
+    o->engine = NMF_ENGINE_TCGEN05;
+    o->device = -1;
+    o->check_every = kCheckEveryDefault;
+    o->use_graph = 1;
+    o->tf32_passes = 3;
+    if (const char* v = std::getenv("NMF_SEMANTICS")) {
+        if (!std::strcmp(v, "refcompat") || !std::strcmp(v, "1")) o->semantics = NMF_REFCOMPAT;
+    }
+    if (const char* v = std::getenv("NMF_ENGINE")) {
+        if (!std::strcmp(v, "simt") || !std::strcmp(v, "1")) o->engine = NMF_ENGINE_SIMT;
+    }
+    o->device = env_int("NMF_DEVICE", o->device);
+    o->check_every = env_int("NMF_CHECK_EVERY", o->check_every);
+    o->use_graph = env_int("NMF_GRAPH", o->use_graph);
+    o->tf32_passes = env_int("NMF_TF32_PASSES", o->tf32_passes);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Part 1: file I/O and update_div
+// ---------------------------------------------------------------------------------------------
+void create_matrix(matrix* A, int rows, int cols, float value) {
+    guarded([&] {
+        NMF_CHECK(A && rows > 0 && cols > 0, "create_matrix: bad arguments");
+        A->dim[0] = rows; A->dim[1] = cols; A->mat_d = nullptr;
+        A->mat = (float*)std::malloc(sizeof(float) * (size_t)rows * cols);
+        NMF_CHECK(A->mat != nullptr, "create_matrix: out of memory");
+        for (size_t i = 0; i < (size_t)rows * cols; ++i) A->mat[i] = value;
+    });
+}
+
+void destroy_matrix(matrix* A) {
+    if (!A) return;
+    std::free(A->mat);
+    if (A->mat_d) cudaFree(A->mat_d);
+    A->mat = nullptr; A->mat_d = nullptr; A->dim[0] = A->dim[1] = 0;
+}
+
+void read_matrix(matrix* A, const char* file) {
+    guarded([&] {
+        NMF_CHECK(A && file, "read_matrix: bad arguments");
+        FILE* fp = std::fopen(file, "rb");
+        NMF_CHECK(fp != nullptr, std::string("read_matrix: cannot open ") + file);   // reference leaves this unchecked
+        int32_t hdr[2] = {0, 0};
+        if (std::fread(hdr, sizeof(int32_t), 2, fp) < 2) { std::fclose(fp); NMF_FAIL("read_matrix: fread error"); }
+        NMF_CHECK(hdr[0] > 0 && hdr[1] > 0, "read_matrix: bad header");
+        const size_t n = (size_t)hdr[0] * (size_t)hdr[1];
+        float* buf = (float*)std::malloc(sizeof(float) * n);
+        if (!buf) { std::fclose(fp); NMF_FAIL("read_matrix: out of memory"); }
+        const size_t got = std::fread(buf, sizeof(float), n, fp);
+        std::fclose(fp);
+        if (got < n) { std::free(buf); NMF_FAIL("read_matrix: fread error"); }
+        for (size_t i = 0; i < n; ++i) if (buf[i] < NMF_EPS_F) buf[i] = NMF_EPS_F;   // set_epsilon after load, nmf.cu:210-211
+        A->mat = buf; A->mat_d = nullptr; A->dim[0] = hdr[0]; A->dim[1] = hdr[1];
+        std::printf("read %s [%ix%i]\n", file, ref_pad32(hdr[0]), ref_pad32(hdr[1]));   // padded dims, nmf.cu:215
+    });
+}
+
+void write_matrix(matrix A, const char* file) {
+    guarded([&] {
+        NMF_CHECK(A.mat && file, "write_matrix: bad arguments");
+        FILE* fp = std::fopen(file, "wb");
+        NMF_CHECK(fp != nullptr, std::string("write_matrix: cannot open ") + file);
+        const int32_t hdr[2] = {A.dim[0], A.dim[1]};
+        const size_t n = (size_t)A.dim[0] * (size_t)A.dim[1];
+        const bool ok = std::fwrite(hdr, sizeof(int32_t), 2, fp) == 2 && std::fwrite(A.mat, sizeof(float), n, fp) == n;
+        std::fclose(fp);
+        NMF_CHECK(ok, "write_matrix: fwrite error");
+        std::printf("write %s [%ix%i]\n", file, A.dim[0], A.dim[1]);                     // nmf.cu:258
+    });
+}
+
+int nmf_update_div_ex(matrix W, matrix H, matrix X, float CONVERGE_THRESH, int max_iter, double t[10],
+                      int verbose, const nmf_options* opt, nmf_result* res) {
+    return guarded([&] {
+        using clk = std::chrono::steady_clock;
+        const auto w0 = clk::now();
+        check_shapes(W, H, X);
+        NMF_CHECK(max_iter >= 0, "update_div: max_iter must be >= 0");
+        const nmf_options o = resolve(opt);
+        nmf_session_impl* s = session_create(W.dim[0], H.dim[1], W.dim[1], 0, H.dim[1], o);
+        try {
+            session_upload(*s, W.mat, H.mat, X.mat);
+            const double setup = std::chrono::duration<double>(clk::now() - w0).count();
+            session_run(*s, CONVERGE_THRESH, max_iter, t, verbose, res);
+            const auto d0 = clk::now();
+            session_download(*s, W.mat, H.mat);
+            if (t) {
+                t[PH_SETUP] = setup + std::chrono::duration<double>(clk::now() - d0).count();
+                t[PH_TOTAL] = std::chrono::duration<double>(clk::now() - w0).count();
+            }
+        } catch (...) { delete s; throw; }
+        delete s;
+    });
+}
+
+void update_div(matrix W, matrix H, matrix X, float CONVERGE_THRESH, int max_iter, double t[10], int verbose) {
+    nmf_update_div_ex(W, H, X, CONVERGE_THRESH, max_iter, t, verbose, nullptr, nullptr);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Part 2: sessions
+// ---------------------------------------------------------------------------------------------
+nmf_session* nmf_session_create(int M, int n_local, int K, long long n_offset, long long n_global,
+                                const nmf_options* opt) {
+    nmf_session* out = nullptr;
+    guarded([&] { out = static_cast<nmf_session*>(session_create(M, n_local, K, n_offset, n_global, resolve(opt))); });
+    return out;
+}
+
+void nmf_session_destroy(nmf_session* s) { delete s; }
+
+int nmf_session_upload(nmf_session* s, const float* W, const float* H, const float* X) {
+    return guarded([&] { NMF_CHECK(s, "NULL session"); session_upload(*s, W, H, X); });
+}
+int nmf_session_download(nmf_session* s, float* W, float* H) {
+    return guarded([&] { NMF_CHECK(s, "NULL session"); session_download(*s, W, H); });
+}
+int nmf_session_fill_uniform(nmf_session* s, unsigned long long seed, int which) {
+    return guarded([&] { NMF_CHECK(s, "NULL session"); session_fill_uniform(*s, seed, which); });
+}
+int nmf_nccl_unique_id(void* id128) { return guarded([&] { nccl_unique_id(id128); }); }
+int nmf_session_join(nmf_session* s, int rank, int nranks, const void* id128) {
+    return guarded([&] { NMF_CHECK(s, "NULL session"); nccl_join(*s, rank, nranks, id128); });
+}
+int nmf_session_run(nmf_session* s, float CONVERGE_THRESH, int max_iter, double t[10], int verbose, nmf_result* res) {
+    return guarded([&] { NMF_CHECK(s, "NULL session"); session_run(*s, CONVERGE_THRESH, max_iter, t, verbose, res); });
+}
+int nmf_session_cost(nmf_session* s, double* cost) {
+    return guarded([&] { NMF_CHECK(s && cost, "NULL argument"); session_cost(*s, cost); });
+}
+
+// ---------------------------------------------------------------------------------------------
+// Part 3: kernel-level entry points for the parity tests
+// ---------------------------------------------------------------------------------------------
+static void with_session(const float* W, const float* H, const float* X, int M, int N, int K, const nmf_options* opt,
+                         const std::function<void(nmf_session_impl&)>& body) {
+    nmf_options o = resolve(opt);
+    o.use_graph = 0;
+    nmf_session_impl* s = session_create(M, N, K, 0, N, o);
+    try { session_upload(*s, W, H, X); body(*s); CUDA_CHECK(cudaStreamSynchronize(s->stream)); }
+    catch (...) { delete s; throw; }
+    delete s;
+}
+
+int nmf_dbg_quotient(const float* W, const float* H, const float* X, float* Y, double* cost,
+                     int M, int N, int K, const nmf_options* opt) {
+    return guarded([&] {
+        with_session(W, H, X, M, N, K, opt, [&](nmf_session_impl& s) {
+            iteration_head(s, cost != nullptr, nullptr);
+            const Dims& d = s.d;
+            std::vector<float> a((size_t)d.Mv * d.Nv), b;
+            if (s.opt.engine == NMF_ENGINE_SIMT) {
+                CUDA_CHECK(cudaMemcpyAsync(a.data(), s.Y, a.size() * 4, cudaMemcpyDeviceToHost, s.stream));
+            } else {   // Y = hi + lo exactly
+                b.resize(a.size());
+                CUDA_CHECK(cudaMemcpyAsync(a.data(), s.Yhi, a.size() * 4, cudaMemcpyDeviceToHost, s.stream));
+                CUDA_CHECK(cudaMemcpyAsync(b.data(), s.Ylo, a.size() * 4, cudaMemcpyDeviceToHost, s.stream));
+            }
+            if (cost) CUDA_CHECK(cudaMemcpyAsync(s.cost_host, s.cost_dev, 8, cudaMemcpyDeviceToHost, s.stream));
+            CUDA_CHECK(cudaStreamSynchronize(s.stream));
+            if (cost) *cost = *s.cost_host;
+            for (int n = 0; n < N; ++n)
+                for (int m = 0; m < M; ++m) {
+                    const size_t i = (size_t)n * d.Mv + m;
+                    Y[(size_t)n * M + m] = b.empty() ? a[i] : a[i] + b[i];
+                }
+        });
+    });
+}
+
+int nmf_dbg_h_step(const float* W, float* H, const float* X, int M, int N, int K, const nmf_options* opt) {
+    return guarded([&] {
+        with_session(W, H, X, M, N, K, opt, [&](nmf_session_impl& s) {
+            iteration_head(s, false, nullptr);
+            if (s.opt.engine == NMF_ENGINE_SIMT) simt_update_h(s.W, s.Y, s.sumW, s.H, s.d, s.stream);
+            else umma::update_h(s);
+            session_download(s, nullptr, H);
+        });
+    });
+}
+
+int nmf_dbg_w_step(float* W, const float* H, const float* X, int M, int N, int K, const nmf_options* opt) {
+    return guarded([&] {
+        with_session(W, H, X, M, N, K, opt, [&](nmf_session_impl& s) {
+            // the W half of iteration_rest, starting from the given H
+            launch_rowsum(s.H, s.rowsum_partials, s.sumH, s.d, s.stream);
+            const float* P = s.packed; int nsplit = 1; size_t stride = 0;
+            if (s.opt.engine == NMF_ENGINE_SIMT) {
+                simt_quotient(s.W, s.H, s.X, s.Y, nullptr, s.d, s.stream);
+                simt_numer(s.Y, s.H, s.packed, s.d, s.stream);
+            } else {
+                umma::quotient(s, false);
+                umma::numer(s);
+                if (s.nsplit > 1) { P = s.Psplit; nsplit = s.nsplit; stride = s.d.szW(); }
+            }
+            launch_update_w(s.W, s.Whi, s.Wlo, P, nsplit, stride, s.sumH, s.d, s.stream);
+            session_download(s, W, nullptr);
+        });
+    });
+}
+
+int nmf_dbg_sums(const float* W, const float* H, float* sumW, float* sumH, int M, int N, int K, const nmf_options* opt) {
+    return guarded([&] {
+        std::vector<float> X((size_t)M * N, 1.0f);
+        with_session(W, H, X.data(), M, N, K, opt, [&](nmf_session_impl& s) {
+            launch_colsum(s.W, s.sumW, s.d, s.stream);
+            launch_rowsum(s.H, s.rowsum_partials, s.sumH, s.d, s.stream);
+            std::vector<float> a(s.d.Kv), b(s.d.Kv);
+            CUDA_CHECK(cudaMemcpyAsync(a.data(), s.sumW, a.size() * 4, cudaMemcpyDeviceToHost, s.stream));
+            CUDA_CHECK(cudaMemcpyAsync(b.data(), s.sumH, b.size() * 4, cudaMemcpyDeviceToHost, s.stream));
+            CUDA_CHECK(cudaStreamSynchronize(s.stream));
+            for (int k = 0; k < K; ++k) {
+                sumW[k] = a[k] < NMF_EPS_F ? NMF_EPS_F : a[k];   // set_epsilon, nmf.cu:135,165
+                sumH[k] = b[k] < NMF_EPS_F ? NMF_EPS_F : b[k];
+            }
+        });
+    });
+}
+
+int nmf_dbg_gemm(int which, const float* A, const float* B, float* C, int M, int N, int K, int passes,
+                 const nmf_options* opt) {
+    return guarded([&] {
+        NMF_CHECK(which >= 0 && which <= 2, "nmf_dbg_gemm: which must be 0..2");
+        NMF_CHECK(M % 32 == 0 && K % 32 == 0 && N % 4 == 0, "nmf_dbg_gemm: needs M,K multiples of 32 and N of 4");
+        const nmf_options o = resolve(opt);
+        if (o.device >= 0) CUDA_CHECK(cudaSetDevice(o.device));
+        // operand shapes (column-major): 0: A MxK, B KxN, C MxN; 1: A MxK, B MxN, C KxN; 2: A MxN, B KxN, C MxK
+        const size_t nA = (which == 2) ? (size_t)M * N : (size_t)M * K;
+        const size_t nB = (which == 1) ? (size_t)M * N : (size_t)K * N;
+        const size_t nC = (which == 0) ? (size_t)M * N : (which == 1 ? (size_t)K * N : (size_t)M * K);
+        float *dA = nullptr, *dB = nullptr, *dC = nullptr;
+        CUDA_CHECK(cudaMalloc((void**)&dA, nA * 4)); CUDA_CHECK(cudaMalloc((void**)&dB, nB * 4));
+        CUDA_CHECK(cudaMalloc((void**)&dC, nC * 4));
+        try {
+            CUDA_CHECK(cudaMemcpy(dA, A, nA * 4, cudaMemcpyHostToDevice));
+            CUDA_CHECK(cudaMemcpy(dB, B, nB * 4, cudaMemcpyHostToDevice));
+            CUDA_CHECK(cudaMemset(dC, 0xFF, nC * 4));
+            umma::dbg_gemm(which, dA, dB, dC, M, N, K, passes, nullptr);
+            CUDA_CHECK(cudaDeviceSynchronize());
+            CUDA_CHECK(cudaMemcpy(C, dC, nC * 4, cudaMemcpyDeviceToHost));
+        } catch (...) { cudaFree(dA); cudaFree(dB); cudaFree(dC); throw; }
+        cudaFree(dA); cudaFree(dB); cudaFree(dC);
+    });
+}
+
+}  // extern "C"

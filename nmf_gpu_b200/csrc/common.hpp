@@ -1,0 +1,109 @@
+// common.hpp — shared host-side declarations of libnmf_b200.so (error convention, device layout,
+// kernel launch prototypes).  Product code: must never include or link anything under oracle/.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <stdexcept>
+#include <string>
+
+#include "../../include/nmf.h"
+
+namespace nmf {
+
+// (float)2.2204E-16 — reference cuda/matrix.cu:10 (fp32 bits 0x257ffea4, not 2^-52).
+#define NMF_EPS_F ((float)(2.2204E-16))
+
+constexpr int kCheckEveryDefault = 25;   // ITER_CHECK, reference cuda/nmf.cu:9
+
+struct Error : std::runtime_error {
+    int code;
+    Error(const std::string& m, int c = 1) : std::runtime_error(m), code(c) {}
+};
+
+[[noreturn]] void fail(const char* file, int line, const std::string& msg, int code = 1);
+
+#define NMF_FAIL(msg) ::nmf::fail(__FILE__, __LINE__, (msg))
+#define NMF_CHECK(cond, msg) do { if (!(cond)) ::nmf::fail(__FILE__, __LINE__, (msg)); } while (0)
+// Reference convention (cuda/error-check.hpp): print "<name> in <file>:<line>" and exit(code).
+// Unlike the reference, launches are polled too (it never calls cudaGetLastError).
+#define CUDA_CHECK(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) \
+    ::nmf::fail(__FILE__, __LINE__, std::string(#expr) + ": " + cudaGetErrorName(e__) + " - " + \
+                cudaGetErrorString(e__), (int)e__); } while (0)
+#define CUDA_CHECK_LAUNCH() CUDA_CHECK(cudaGetLastError())
+
+inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+inline long long round_up_ll(long long v, long long m) { return (v + m - 1) / m * m; }
+
+// Reference padding rule, cuda/matrix.cu:88-95 (dims equal to 1 are not padded).
+inline int ref_pad32(int v) { return (v != 1 && v % 32 != 0) ? v + (32 - v % 32) : v; }
+
+// Extents of one rank's shard as the kernels see them.
+//   logical   : M, N (local columns), K
+//   "valid"   : Mv, Nv, Kv — the index ranges the kernels iterate over.
+//       exact     : Mv = round_up(M,32), Kv = round_up(K,32) with ZERO fill (rows of zeros are
+//                   fixed points of the update and contribute nothing), Nv = N.
+//       refcompat : the reference's padded dims (cuda/matrix.cu:88-95) with EPS fill, because its
+//                   clamp runs over the whole padded buffer (cuda/nmf.cu:211).
+//   leading dimensions: ldM = Mv (W, X, Y, P), ldK = Kv (H) — multiples of 32 floats (128 B).
+struct Dims {
+    int M = 0, N = 0, K = 0;
+    int Mv = 0, Nv = 0, Kv = 0;
+    long long n_offset = 0, n_global = 0;
+    int refcompat = 0;
+    int w_divide = 1;        // 0 iff refcompat and rows_padded(W) > 1024 (cuda/matrix.cu:212-217)
+    size_t szW() const { return (size_t)Mv * Kv; }
+    size_t szH() const { return (size_t)Kv * Nv; }
+    size_t szX() const { return (size_t)Mv * Nv; }
+};
+
+Dims make_dims(int M, int n_local, int K, long long n_offset, long long n_global, int semantics);
+
+// ---------------------------------------------------------------------------------------------
+// Small kernels (kernels_small.cu).  All take the stream explicitly; none synchronises.
+// ---------------------------------------------------------------------------------------------
+// a[i] = max(a[i], EPS) over rows x cols of a column-major buffer with leading dimension ld.
+void launch_clamp_eps(float* a, int rows, int cols, int ld, cudaStream_t st);
+// Fill rows [r0,r1) x cols [c0,c1) with value (used for the refcompat EPS padding).
+void launch_fill_region(float* a, int ld, int r0, int r1, int c0, int c1, float value, cudaStream_t st);
+// uniform(0,1) from a hash of (seed, tag, global row, global col); rows x cols, then clampE.
+void launch_fill_uniform(float* a, int rows, int cols, int ld, long long col_offset,
+                         unsigned long long seed, int tag, cudaStream_t st);
+// hi = x with the low 13 mantissa bits cleared (exactly representable in TF32), lo = x - hi (exact).
+void launch_split_tf32(const float* x, float* hi, float* lo, size_t n, cudaStream_t st);
+
+// sumW[k] = sum_m W[m,k]  (R1; reference: Matrix::sum_cols + reduce2d, cuda/matrix.cu:261-377,642-687)
+// refcompat: only rows m with (m mod 64) in {0,1,2,4,8,16,32} (the reference's stale-read tail).
+// Result is NOT clamped; consumers apply max(.,EPS) (reference: sumW->set_epsilon, nmf.cu:135).
+void launch_colsum(const float* W, float* sumW, const Dims& d, cudaStream_t st);
+// sumH[k] = sum_n H[k,n]  (R2; reference: Matrix::sum_rows + reduce2d_strided, matrix.cu:379-503,689-735)
+// Two passes: per-column-block partials, then an ordered finish (deterministic, no float atomics).
+// `partials` must hold rowsum_partial_count(d) * d.Kv floats.
+int  rowsum_partial_count(const Dims& d);
+void launch_rowsum(const float* H, float* partials, float* sumH, const Dims& d, cudaStream_t st);
+
+// W[m,k] <- W[m,k] * ((sum_s P[s][m,k]) / max(sumH[k],EPS))   (reference: row_divide + element_multiply,
+// cuda/nmf.cu:172-175).  The divide is skipped when !d.w_divide.  Optionally writes the TF32 split.
+void launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nsplit, size_t split_stride,
+                     const float* sumH, const Dims& d, cudaStream_t st);
+
+// out[e] = sum_s P[s][e] in split order (multi-GPU: fold the local splits before the allreduce).
+void launch_fold_splits(const float* P, int nsplit, size_t split_stride, float* out, size_t n, cudaStream_t st);
+
+// cost = sum of `n` double partials (ordered).
+void launch_sum_partials(const double* partials, int n, double* out, cudaStream_t st);
+
+// ---------------------------------------------------------------------------------------------
+// SIMT engine (kernels_simt.cu): fp32 FFMA GEMMs with the same fused epilogues.  Bring-up aid.
+// ---------------------------------------------------------------------------------------------
+int  simt_cost_partial_count(const Dims& d);
+// Y = X ./ max(W*H,EPS); if cost_partials != nullptr also per-block KL partial sums.
+void simt_quotient(const float* W, const float* H, const float* X, float* Y, double* cost_partials,
+                   const Dims& d, cudaStream_t st);
+// H <- H .* ((W'*Y) ./ max(sumW,EPS))
+void simt_update_h(const float* W, const float* Y, const float* sumW, float* H, const Dims& d, cudaStream_t st);
+// P = Y*H'
+void simt_numer(const float* Y, const float* H, float* P, const Dims& d, cudaStream_t st);
+
+}  // namespace nmf

@@ -1,0 +1,250 @@
+// kernels_small.cu — HBM-bound helper kernels: clamp, fills, TF32 split, the W column sums (R1),
+// the H row sums (R2), the W multiplicative update, ordered partial-sum finishes.
+// All reductions are warp-shuffle trees with a fixed order (no float atomics): run-to-run
+// bit-reproducible, which the 1e-4 @ 100 iterations parity budget needs (SURVEY.md §7 "Determinism").
+#include "common.hpp"
+
+namespace nmf {
+
+namespace {
+
+__device__ __forceinline__ float clampE(float v) { return v < NMF_EPS_F ? NMF_EPS_F : v; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// The reference's reduce2d tail (cuda/matrix.cu:676-683) reads stale shared memory; what its
+// "sum" covers is exactly the indices with (i mod 64) in {0,1,2,4,8,16,32}  (SURVEY.md §0.2).
+__device__ __forceinline__ bool ref_sum_mask(long long i) {
+    const unsigned r = (unsigned)(i & 63);
+    return r == 0 || (r & (r - 1)) == 0;     // 0 or a power of two < 64
+}
+
+__global__ void k_clamp_eps(float* __restrict__ a, int rows, int cols, int ld) {
+    const size_t total = (size_t)rows * cols;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (size_t)gridDim.x * blockDim.x) {
+        const size_t c = i / rows, r = i - c * rows;
+        float* p = a + c * (size_t)ld + r;
+        *p = clampE(*p);
+    }
+}
+
+__global__ void k_fill_region(float* __restrict__ a, int ld, int r0, int r1, int c0, int c1, float value) {
+    const int nr = r1 - r0;
+    const size_t total = (size_t)nr * (c1 - c0);
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (size_t)gridDim.x * blockDim.x) {
+        const size_t c = i / nr, r = i - c * nr;
+        a[(c0 + c) * (size_t)ld + r0 + r] = value;
+    }
+}
+
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {   // splitmix64 finaliser
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+__global__ void k_fill_uniform(float* __restrict__ a, int rows, int cols, int ld, long long col_offset,
+                               unsigned long long seed, int tag) {
+    const size_t total = (size_t)rows * cols;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (size_t)gridDim.x * blockDim.x) {
+        const size_t c = i / rows, r = i - c * rows;
+        const unsigned long long gc = (unsigned long long)(col_offset + (long long)c);
+        unsigned long long h = mix64(seed * 0x9E3779B97F4A7C15ull + (unsigned long long)tag);
+        h = mix64(h ^ (gc * 0xD1B54A32D192ED03ull + (unsigned long long)r));
+        const float u = (float)(h >> 40) * (1.0f / 16777216.0f);   // 24 random bits -> [0,1)
+        a[c * (size_t)ld + r] = clampE(u);
+    }
+}
+
+__global__ void k_split_tf32(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo, size_t n) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float v = x[i];
+        const float h = __uint_as_float(__float_as_uint(v) & 0xFFFFE000u);
+        hi[i] = h;
+        lo[i] = v - h;
+    }
+}
+
+// R1: one block per column of W (contiguous, coalesced), 256 threads, shuffle tree.
+__global__ void __launch_bounds__(256) k_colsum(const float* __restrict__ W, float* __restrict__ sumW,
+                                                int Mv, int ld, int refcompat) {
+    const float* col = W + (size_t)blockIdx.x * ld;
+    float s = 0.0f;
+    if (refcompat) {
+        for (int m = threadIdx.x; m < Mv; m += 256) if (ref_sum_mask(m)) s += col[m];
+    } else {
+        for (int m = threadIdx.x; m < Mv; m += 256) s += col[m];
+    }
+    __shared__ float part[8];
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        float v = threadIdx.x < 8 ? part[threadIdx.x] : 0.0f;
+        v = warp_sum(v);
+        if (threadIdx.x == 0) sumW[blockIdx.x] = v;
+    }
+}
+
+// R2 pass 1: block = 32 (rows k, contiguous => coalesced 128 B per warp) x 8 (column lanes);
+// each block covers kRowsumChunk columns.  partial[chunk][k].
+constexpr int kRowsumChunk = 512;
+__global__ void __launch_bounds__(256) k_rowsum_partial(const float* __restrict__ H, float* __restrict__ partials,
+                                                        int Kv, int Nv, long long n_offset, int refcompat) {
+    const int k = blockIdx.x * 32 + threadIdx.x;
+    const int n0 = blockIdx.y * kRowsumChunk;
+    const int n1 = min(Nv, n0 + kRowsumChunk);
+    float s = 0.0f;
+    if (k < Kv) {
+        for (int n = n0 + threadIdx.y; n < n1; n += 8) {
+            if (!refcompat || ref_sum_mask(n_offset + n)) s += H[(size_t)n * Kv + k];
+        }
+    }
+    __shared__ float sm[8][33];
+    sm[threadIdx.y][threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.y == 0 && k < Kv) {
+        float t = 0.0f;
+        #pragma unroll
+        for (int j = 0; j < 8; ++j) t += sm[j][threadIdx.x];
+        partials[(size_t)blockIdx.y * Kv + k] = t;
+    }
+}
+
+// R2 pass 2: ordered sum over the chunks.
+__global__ void k_rowsum_finish(const float* __restrict__ partials, float* __restrict__ sumH, int Kv, int nchunks) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= Kv) return;
+    float s = 0.0f;
+    for (int c = 0; c < nchunks; ++c) s += partials[(size_t)c * Kv + k];
+    sumH[k] = s;
+}
+
+// W update: one thread per 4 consecutive rows of one column (float4, ld is a multiple of 32).
+__global__ void __launch_bounds__(256) k_update_w(float* __restrict__ W, float* __restrict__ Whi, float* __restrict__ Wlo,
+                                                  const float* __restrict__ P, int nsplit, size_t split_stride,
+                                                  const float* __restrict__ sumH, int Mv, int Kv, int divide) {
+    const size_t total4 = (size_t)Mv * Kv / 4;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t e = i * 4;
+        const int k = (int)(e / Mv);
+        float4 acc = *reinterpret_cast<const float4*>(P + e);
+        for (int s = 1; s < nsplit; ++s) {                       // ordered: split 0,1,2,...
+            const float4 p = *reinterpret_cast<const float4*>(P + (size_t)s * split_stride + e);
+            acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+        }
+        if (divide) {                                            // row_div, cuda/matrix.cu:220-224
+            const float d = clampE(sumH[k]);
+            acc.x = acc.x / d; acc.y = acc.y / d; acc.z = acc.z / d; acc.w = acc.w / d;
+        }
+        float4 w = *reinterpret_cast<float4*>(W + e);
+        w.x *= acc.x; w.y *= acc.y; w.z *= acc.z; w.w *= acc.w;  // vec_mul, cuda/matrix.cu:174-180
+        *reinterpret_cast<float4*>(W + e) = w;
+        if (Whi != nullptr) {
+            float4 h, l;
+            h.x = __uint_as_float(__float_as_uint(w.x) & 0xFFFFE000u); l.x = w.x - h.x;
+            h.y = __uint_as_float(__float_as_uint(w.y) & 0xFFFFE000u); l.y = w.y - h.y;
+            h.z = __uint_as_float(__float_as_uint(w.z) & 0xFFFFE000u); l.z = w.z - h.z;
+            h.w = __uint_as_float(__float_as_uint(w.w) & 0xFFFFE000u); l.w = w.w - h.w;
+            *reinterpret_cast<float4*>(Whi + e) = h;
+            *reinterpret_cast<float4*>(Wlo + e) = l;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_fold_splits(const float* __restrict__ P, int nsplit, size_t split_stride,
+                                                     float* __restrict__ out, size_t n4) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        float4 acc = *reinterpret_cast<const float4*>(P + i * 4);
+        for (int s = 1; s < nsplit; ++s) {
+            const float4 p = *reinterpret_cast<const float4*>(P + (size_t)s * split_stride + i * 4);
+            acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+        }
+        *reinterpret_cast<float4*>(out + i * 4) = acc;
+    }
+}
+
+__global__ void k_sum_partials(const double* __restrict__ partials, int n, double* __restrict__ out) {
+    // one warp; lane-strided ordered sums then a fixed shuffle tree: deterministic.
+    double s = 0.0;
+    for (int i = threadIdx.x; i < n; i += 32) s += partials[i];
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (threadIdx.x == 0) *out = s;
+}
+
+inline int grid_for(size_t total, int block, int max_blocks = 148 * 16) {
+    size_t g = (total + block - 1) / block;
+    if (g < 1) g = 1;
+    if (g > (size_t)max_blocks) g = max_blocks;
+    return (int)g;
+}
+
+}  // namespace
+
+void launch_clamp_eps(float* a, int rows, int cols, int ld, cudaStream_t st) {
+    if ((size_t)rows * cols == 0) return;
+    k_clamp_eps<<<grid_for((size_t)rows * cols, 256), 256, 0, st>>>(a, rows, cols, ld);
+    CUDA_CHECK_LAUNCH();
+}
+
+void launch_fill_region(float* a, int ld, int r0, int r1, int c0, int c1, float value, cudaStream_t st) {
+    if (r1 <= r0 || c1 <= c0) return;
+    k_fill_region<<<grid_for((size_t)(r1 - r0) * (c1 - c0), 256), 256, 0, st>>>(a, ld, r0, r1, c0, c1, value);
+    CUDA_CHECK_LAUNCH();
+}
+
+void launch_fill_uniform(float* a, int rows, int cols, int ld, long long col_offset,
+                         unsigned long long seed, int tag, cudaStream_t st) {
+    if ((size_t)rows * cols == 0) return;
+    k_fill_uniform<<<grid_for((size_t)rows * cols, 256), 256, 0, st>>>(a, rows, cols, ld, col_offset, seed, tag);
+    CUDA_CHECK_LAUNCH();
+}
+
+void launch_split_tf32(const float* x, float* hi, float* lo, size_t n, cudaStream_t st) {
+    if (n == 0) return;
+    k_split_tf32<<<grid_for(n, 256), 256, 0, st>>>(x, hi, lo, n);
+    CUDA_CHECK_LAUNCH();
+}
+
+void launch_colsum(const float* W, float* sumW, const Dims& d, cudaStream_t st) {
+    k_colsum<<<d.Kv, 256, 0, st>>>(W, sumW, d.Mv, d.Mv, d.refcompat);
+    CUDA_CHECK_LAUNCH();
+}
+
+int rowsum_partial_count(const Dims& d) { return (d.Nv + kRowsumChunk - 1) / kRowsumChunk; }
+
+void launch_rowsum(const float* H, float* partials, float* sumH, const Dims& d, cudaStream_t st) {
+    const int nch = rowsum_partial_count(d);
+    dim3 grid((d.Kv + 31) / 32, nch), block(32, 8);
+    k_rowsum_partial<<<grid, block, 0, st>>>(H, partials, d.Kv, d.Nv, d.n_offset, d.refcompat);
+    CUDA_CHECK_LAUNCH();
+    k_rowsum_finish<<<(d.Kv + 127) / 128, 128, 0, st>>>(partials, sumH, d.Kv, nch);
+    CUDA_CHECK_LAUNCH();
+}
+
+void launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nsplit, size_t split_stride,
+                     const float* sumH, const Dims& d, cudaStream_t st) {
+    k_update_w<<<grid_for(d.szW() / 4, 256), 256, 0, st>>>(W, Whi, Wlo, P, nsplit, split_stride, sumH,
+                                                           d.Mv, d.Kv, d.w_divide);
+    CUDA_CHECK_LAUNCH();
+}
+
+void launch_fold_splits(const float* P, int nsplit, size_t split_stride, float* out, size_t n, cudaStream_t st) {
+    k_fold_splits<<<grid_for(n / 4, 256), 256, 0, st>>>(P, nsplit, split_stride, out, n / 4);
+    CUDA_CHECK_LAUNCH();
+}
+
+void launch_sum_partials(const double* partials, int n, double* out, cudaStream_t st) {
+    k_sum_partials<<<1, 32, 0, st>>>(partials, n, out);
+    CUDA_CHECK_LAUNCH();
+}
+
+}  // namespace nmf

@@ -1,0 +1,75 @@
+// session.hpp — one rank's device-resident NMF problem and the iteration driver.
+#pragma once
+#include "common.hpp"
+
+namespace nmf {
+
+namespace umma { struct Plan; }
+
+struct Nccl;   // dlopen'ed NCCL entry points + communicator (dist.cpp)
+
+struct nmf_session_impl {
+    nmf_options opt{};
+    Dims d{};
+    int device = 0;
+    cudaStream_t stream = nullptr;
+
+    // fp32 masters (column-major, ld = Mv / Kv)
+    float *W = nullptr, *H = nullptr, *X = nullptr;
+    // quotient Y = X ./ max(WH,EPS): SIMT engine keeps one fp32 copy, tcgen05 engine the TF32 split
+    float *Y = nullptr, *Yhi = nullptr, *Ylo = nullptr;
+    // TF32 splits of the small operands (tcgen05 engine)
+    float *Whi = nullptr, *Wlo = nullptr, *Hhi = nullptr, *Hlo = nullptr;
+    // sums and the packed allreduce buffer [ numerator P (Mv*Kv) | sumH (Kv) ]
+    float *sumW = nullptr, *packed = nullptr, *sumH = nullptr /* = packed + Mv*Kv */;
+    float *Psplit = nullptr; int nsplit = 1;      // split-N partial numerators (tcgen05 engine)
+    float *rowsum_partials = nullptr;
+    double *cost_partials = nullptr; int n_cost_partials = 0;
+    double *cost_dev = nullptr, *cost_host = nullptr /* pinned */;
+
+    umma::Plan* plan = nullptr;
+
+    // multi-GPU
+    Nccl* nccl = nullptr; int rank = 0, nranks = 1;
+
+    // graphs (one iteration; and the iteration minus its leading colsum+quotient)
+    cudaGraphExec_t g_full = nullptr, g_rest = nullptr;
+    long long launches_full = 0, launches_rest = 0, launches_head = 0;
+    long long launches = 0;    // running count of this library's kernel launches
+
+    ~nmf_session_impl();
+};
+
+// phases for t[10]
+enum Phase { PH_QUOT = 0, PH_SUMS = 2, PH_GEMM2 = 3, PH_UPDW = 5, PH_COST = 6, PH_COMM = 7, PH_SETUP = 8, PH_TOTAL = 9 };
+
+struct PhaseTimer;   // session.cu
+
+// iteration pieces (session.cu)
+void iteration_head(nmf_session_impl& s, bool with_cost, PhaseTimer* pt);   // colsum(W); Y = quotient (+cost partials)
+void iteration_rest(nmf_session_impl& s, PhaseTimer* pt);                   // H update; rowsum; quotient; numerator; [allreduce]; W update
+
+// NCCL (dist.cpp)
+int  nccl_unique_id(void* id128);
+void nccl_join(nmf_session_impl& s, int rank, int nranks, const void* id128);
+void nccl_allreduce_f32(nmf_session_impl& s, float* buf, size_t n);
+void nccl_allreduce_f64(nmf_session_impl& s, double* buf, size_t n);
+void nccl_destroy(Nccl* n);
+
+namespace umma {
+// tcgen05 engine (kernels_umma.cu)
+Plan* plan_create(nmf_session_impl& s);
+void  plan_destroy(Plan* p);
+int   cost_partial_count(const Dims& d);
+int   numer_splits(const Dims& d);
+void  quotient(nmf_session_impl& s, bool with_cost);
+void  update_h(nmf_session_impl& s);
+void  numer(nmf_session_impl& s);
+// raw contraction for descriptor bring-up (nmf_dbg_gemm)
+void  dbg_gemm(int which, const float* dA, const float* dB, float* dC, int M, int N, int K, int passes,
+               cudaStream_t st);
+}  // namespace umma
+
+}  // namespace nmf
+
+struct nmf_session : nmf::nmf_session_impl {};

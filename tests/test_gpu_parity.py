@@ -1,0 +1,189 @@
+"""GPU parity tests: the CUDA path (through the C ABI of libnmf_b200.so) against the CPU oracle, the
+reference's golden vectors and size-independent properties.  Run on the B200 box: pytest -m gpu.
+
+Tolerances (BASELINE.json north_star / BASELINE.md "Parity gates"):
+  exact     : max |d| / max(|ref|, 1e-6 max|ref|) <= 1e-4 on W and H after 100 iterations,
+              KL divergence within 1e-5 relative.
+  refcompat : KL within 1e-5 relative, identical surviving components, Frobenius-relative <= 2e-3
+              (the trajectory is ill-conditioned there: fp32 vs fp64 runs of the same arithmetic
+              already differ by ~1e-2 elementwise).
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from util import fro_rel, max_rel, rand_problem, survivors
+
+ENGINES = ["tcgen05", "simt"]
+GOLDEN_SURVIVORS = [1, 22, 30, 34, 43, 45, 57, 70, 88, 89, 93, 96, 110, 113, 118, 121, 126]
+
+
+@pytest.fixture(scope="module")
+def api():
+    import nmf_gpu_b200.api as a
+    a.lib()
+    return a
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    from oracle import oracle as o
+    o.lib()
+    return o
+
+
+# ---------------------------------------------------------------------------------------------
+# kernel level
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("which", [0, 1, 2])
+@pytest.mark.parametrize("shape", [(128, 256, 64), (160, 100, 96), (384, 520, 160), (32, 4, 32)])
+def test_umma_raw_gemm_3xtf32(api, which, shape):
+    """the tensor-core contraction itself, all three operand-major combinations, ragged tiles"""
+    M, N, K = shape
+    rng = np.random.RandomState(which * 7 + M)
+    sa, sb = {0: ((M, K), (K, N)), 1: ((M, K), (M, N)), 2: ((M, N), (K, N))}[which]
+    A = np.asfortranarray(rng.rand(*sa).astype(np.float32) - 0.25)
+    B = np.asfortranarray(rng.rand(*sb).astype(np.float32) - 0.25)
+    C = api.dbg_gemm(which, A, B, M, N, K, passes=3)
+    A64, B64 = A.astype(np.float64), B.astype(np.float64)
+    ref = {0: lambda: A64 @ B64, 1: lambda: A64.T @ B64, 2: lambda: A64 @ B64.T}[which]()
+    assert np.abs(C - ref).max() / np.abs(ref).max() < 2e-6      # fp32-class accuracy
+    C1 = api.dbg_gemm(which, A, B, M, N, K, passes=1)
+    e1 = np.abs(C1 - ref).max() / np.abs(ref).max()
+    assert 1e-6 < e1 < 5e-3                                        # single-pass TF32 is visibly coarser
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("shape", [(256, 512, 64), (130, 70, 40), (513, 300, 40), (33, 17, 5)])
+def test_quotient_and_cost(api, oracle, engine, shape):
+    M, N, K = shape
+    W, H, X = rand_problem(M, N, K, seed=M + N)
+    X[::7, ::5] = 0.0                                              # zeros are clamped to EPS on load
+    Y, cost = api.dbg_quotient(W, H, X, api.options(engine=engine))
+    Yref = oracle.quotient(W, H, X, acc64=True)
+    assert max_rel(Y, Yref) < 5e-6
+    ref_cost = oracle.kl(W, H, X)
+    assert abs(cost - ref_cost) / abs(ref_cost) < 1e-5
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("mode", ["exact", "refcompat"])
+def test_sums(api, engine, mode):
+    W, H, _ = rand_problem(200, 333, 48, seed=5)
+    sw, sh = api.dbg_sums(W, H, api.options(semantics=mode, engine=engine))
+    if mode == "exact":
+        assert np.allclose(sw, W.astype(np.float64).sum(0), rtol=1e-5)
+        assert np.allclose(sh, H.astype(np.float64).sum(1), rtol=1e-5)
+    else:
+        eps = np.float32(2.2204e-16)
+        Wp = np.full((224, 64), eps, np.float64); Wp[:200, :48] = W
+        Hp = np.full((64, 352), eps, np.float64); Hp[:48, :333] = H
+        mask = lambda n: np.isin(np.arange(n) % 64, [0, 1, 2, 4, 8, 16, 32])
+        assert np.allclose(sw, Wp[mask(224)].sum(0)[:48], rtol=1e-5)
+        assert np.allclose(sh, Hp[:, mask(352)].sum(1)[:48], rtol=1e-5)
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("mode", ["exact", "refcompat"])
+@pytest.mark.parametrize("shape", [(256, 512, 64), (130, 70, 40), (1100, 90, 33)])
+def test_half_steps(api, oracle, engine, mode, shape):
+    M, N, K = shape
+    W, H, X = rand_problem(M, N, K, seed=K)
+    opt = api.options(semantics=mode, engine=engine)
+    H1 = api.dbg_h_step(W, H, X, opt)
+    assert max_rel(H1, oracle.h_step(W, H, X, mode, acc64=True)) < 2e-5
+    W1 = api.dbg_w_step(W, H, X, opt)
+    assert max_rel(W1, oracle.w_step(W, H, X, mode, acc64=True)) < 2e-5
+
+
+# ---------------------------------------------------------------------------------------------
+# update_div end to end
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("engine", ENGINES)
+def test_c1_exact_100_iterations(api, oracle, c1, engine):
+    """BASELINE config C1, exact semantics: the north-star tolerance."""
+    W = c1["W"].copy(order="F"); H = c1["H"].copy(order="F")
+    res = api.update_div(W, H, c1["X"], 0.0, 100, opt=api.options(engine=engine))
+    assert res.iterations == 100
+    W64, H64, _, cost64 = oracle.update_div(c1["W"], c1["H"], c1["X"], 0.0, 100, "exact", acc64=True)
+    assert max_rel(W, W64) <= 1e-4 and max_rel(H, H64) <= 1e-4
+    cost = oracle.kl(W, H, c1["X"])
+    assert abs(cost - cost64) / cost64 <= 1e-5
+    assert abs(cost - 105982.05) / 105982.05 < 1e-5                 # BASELINE.md known answer
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+def test_c1_refcompat_matches_reference_golden(api, oracle, c1, engine):
+    """200 iterations, thresh 0 (cuda/nmf.cu:10-11) == the reference's Wtest.bin / Htest.bin"""
+    W = c1["W"].copy(order="F"); H = c1["H"].copy(order="F")
+    res = api.update_div(W, H, c1["X"], 0.0, 200, opt=api.options(semantics="refcompat", engine=engine))
+    assert res.iterations == 200
+    gold = oracle.kl(c1["Wtest"], c1["Htest"], c1["X"])
+    assert abs(oracle.kl(W, H, c1["X"]) - gold) / gold <= 1e-5
+    assert survivors(W) == GOLDEN_SURVIVORS
+    assert fro_rel(W, c1["Wtest"]) <= 2e-3 and fro_rel(H, c1["Htest"]) <= 2e-3
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+def test_c2_shape_small_k(api, oracle, engine):
+    """ISMIR shape family (M=513, K=40: ragged rows, K padded to 64), fewer columns/iterations"""
+    W, H, X = rand_problem(513, 2000, 40, seed=1)
+    Wd = W.copy(order="F"); Hd = H.copy(order="F")
+    api.update_div(Wd, Hd, X, 0.0, 30, opt=api.options(engine=engine))
+    Wo, Ho, _, cost = oracle.update_div(W, H, X, 0.0, 30, "exact", acc64=True)
+    assert max_rel(Wd, Wo) <= 1e-4 and max_rel(Hd, Ho) <= 1e-4
+    assert abs(oracle.kl(Wd, Hd, X) - cost) / cost <= 1e-5
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+def test_convergence_threshold_and_cost(api, oracle, engine):
+    rng = np.random.RandomState(2)
+    X = np.asfortranarray((rng.rand(96, 4) @ rng.rand(4, 80)).astype(np.float32))
+    W, H, _ = rand_problem(96, 80, 4, seed=9)
+    Wd = W.copy(order="F"); Hd = H.copy(order="F")
+    res = api.update_div(Wd, Hd, X, 0.5, 400, opt=api.options(engine=engine))
+    _, _, it, cost = oracle.update_div(W, H, X, 0.5, 400, "exact")
+    assert res.converged == 1 and res.iterations == it
+    assert abs(res.cost - cost) / cost < 1e-4
+
+
+def test_t10_and_graph_vs_eager(api, c1):
+    """per-phase timers are filled; graph replay and eager launches give identical bits"""
+    W0, H0, X = c1["W"][:, :64], c1["H"][:64], c1["X"]
+    Wa = W0.copy(order="F"); Ha = H0.copy(order="F")
+    Wb = W0.copy(order="F"); Hb = H0.copy(order="F")
+    t = np.zeros(10)
+    api.update_div(Wa, Ha, X, 0.0, 10, t=t)                       # timed => eager
+    api.update_div(Wb, Hb, X, 0.0, 10)                            # graph
+    assert np.array_equal(Wa, Wb) and np.array_equal(Ha, Hb)
+    assert t[0] > 0 and t[2] > 0 and t[3] > 0 and t[5] > 0 and t[9] >= t[0] + t[3]
+
+
+def test_full_size_properties(api):
+    """a size the oracle cannot follow: KL decreases monotonically, factors stay finite and >= 0,
+    and the device generator does not depend on how columns are sharded"""
+    M, N, K = 2048, 16384, 128
+    with api.Session(M, N, K) as s:
+        s.fill_uniform(4)
+        prev = s.cost()
+        for _ in range(3):
+            s.run(0.0, 2)
+            c = s.cost()
+            assert np.isfinite(c) and c <= prev * (1 + 1e-6)
+            prev = c
+        W, H = s.download()
+    assert np.isfinite(W).all() and np.isfinite(H).all() and (W >= 0).all() and (H >= 0).all()
+    with api.Session(M, N // 2, K, n_offset=N // 2, n_global=N) as s2:
+        s2.fill_uniform(4, which=2)
+        _, Hhalf = s2.download()
+    with api.Session(M, N, K) as s3:
+        s3.fill_uniform(4, which=2)
+        _, Hfull = s3.download()
+    assert np.array_equal(Hhalf, Hfull[:, N // 2:])
+
+
+def test_shape_mismatch_raises(api):
+    W, H, X = rand_problem(64, 64, 32, seed=1)
+    with pytest.raises(api.NmfError):
+        api.update_div(W, H[:, :10].copy(order="F"), X, 0.0, 1)
