@@ -3,6 +3,7 @@
 // All reductions are warp-shuffle trees with a fixed order (no float atomics): run-to-run
 // bit-reproducible, which the 1e-4 @ 100 iterations parity budget needs (SURVEY.md §7 "Determinism").
 #include "common.hpp"
+#include "tf32.cuh"
 
 namespace nmf {
 
@@ -65,10 +66,10 @@ __global__ void k_fill_uniform(float* __restrict__ a, int rows, int cols, int ld
 
 __global__ void k_split_tf32(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo, size_t n) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        const float v = x[i];
-        const float h = __uint_as_float(__float_as_uint(v) & 0xFFFFE000u);
+        float h, l;
+        tf32_split(x[i], h, l);
         hi[i] = h;
-        lo[i] = v - h;
+        lo[i] = l;
     }
 }
 
@@ -149,10 +150,8 @@ __global__ void __launch_bounds__(256) k_update_w(float* __restrict__ W, float* 
         *reinterpret_cast<float4*>(W + e) = w;
         if (Whi != nullptr) {
             float4 h, l;
-            h.x = __uint_as_float(__float_as_uint(w.x) & 0xFFFFE000u); l.x = w.x - h.x;
-            h.y = __uint_as_float(__float_as_uint(w.y) & 0xFFFFE000u); l.y = w.y - h.y;
-            h.z = __uint_as_float(__float_as_uint(w.z) & 0xFFFFE000u); l.z = w.z - h.z;
-            h.w = __uint_as_float(__float_as_uint(w.w) & 0xFFFFE000u); l.w = w.w - h.w;
+            tf32_split(w.x, h.x, l.x); tf32_split(w.y, h.y, l.y);
+            tf32_split(w.z, h.z, l.z); tf32_split(w.w, h.w, l.w);
             *reinterpret_cast<float4*>(Whi + e) = h;
             *reinterpret_cast<float4*>(Wlo + e) = l;
         }

@@ -38,6 +38,26 @@ def one_case(which, passes, variant, M, N, K):
     print("CASE " + json.dumps(out))
 
 
+def acc_probe(R):
+    """How does the tensor core round its fp32 accumulator?  Positive inputs with 6-bit mantissas:
+    every product is exact in fp32, the split's lo parts are zero, so any error is accumulation
+    rounding.  Mean signed error ~0 => round-to-nearest; negative ~ -n/2 ulp => truncation."""
+    import nmf_gpu_b200.api as api
+    rng = np.random.RandomState(5)
+    q = lambda a: (np.floor(a * 64) / 64 + 1.0 / 64).astype(np.float32)       # in (0,1], 6 bits
+    K, N = 128, 256
+    A = np.asfortranarray(q(rng.rand(R, K))); B = np.asfortranarray(q(rng.rand(R, N)))
+    out = dict(probe="acc", R=R)
+    for passes in (1, 3):
+        C = api.dbg_gemm(1, A, B, R, N, K, passes)
+        ref = A.astype(np.float64).T @ B.astype(np.float64)
+        rel = (C.astype(np.float64) - ref) / ref
+        out[f"p{passes}_mean_signed"] = float(rel.mean()); out[f"p{passes}_max_abs"] = float(np.abs(rel).max())
+    # fp32 round-to-nearest sequential reference for scale
+    out["ulp"] = 2.0 ** -24
+    print("CASE " + json.dumps(out))
+
+
 def tf32_rounding_probe():
     """Does tcgen05.mma.kind::tf32 truncate or round the 13 dropped mantissa bits? (1-pass, raw inputs
     are pre-masked by the split kernel, so feed values whose lo part is exactly half an ulp...)"""
@@ -60,8 +80,11 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "case":
         one_case(*[int(v) for v in sys.argv[2:8]])
         sys.exit(0)
-    for c in CASES:
-        cmd = [sys.executable, os.path.abspath(__file__), "case"] + [str(v) for v in c]
+    if len(sys.argv) > 1 and sys.argv[1] == "acc":
+        acc_probe(int(sys.argv[2]))
+        sys.exit(0)
+    for c in CASES + [("acc", 512), ("acc", 4096), ("acc", 16384)]:
+        cmd = [sys.executable, os.path.abspath(__file__)] + (["case"] if c[0] != "acc" else []) + [str(v) for v in c]
         try:
             r = subprocess.run(cmd, capture_output=True, text=True, timeout=120)
             lines = [l for l in r.stdout.splitlines() if l.startswith("CASE ")]
