@@ -34,6 +34,7 @@ WORKLOADS = {                     # name: (M, N, K, seed, description)
     "c3s": (2049, 262144, 128, 3, "C3-shape 2049x262144 K=128"),
     "c2": (513, 20000, 40, 1, "C2 audio spectrogram 513x20000 K=40"),
     "c1": (4096, 350, 128, 0, "C1 bundled shape 4096x350 K=128"),
+    "mid": (8192, 32768, 256, 7, "mid 8192x32768 K=256 (profiling size)"),
     "tiny": (1024, 4096, 64, 9, "tiny 1024x4096 K=64"),
 }
 

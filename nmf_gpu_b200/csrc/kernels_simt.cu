@@ -53,6 +53,11 @@ __global__ void __launch_bounds__(NT) k_simt_gemm(SimtArgs a) {
             Bs[r2][jj] = (gj < a.J && gr2 < a.R) ? a.B[(long long)gr2 * a.sBr + (long long)gj * a.sBj] : 0.0f;
         }
         __syncthreads();
+        float part[4][4];
+        #pragma unroll
+        for (int p2 = 0; p2 < 4; ++p2)
+            #pragma unroll
+            for (int q2 = 0; q2 < 4; ++q2) part[p2][q2] = 0.0f;
         #pragma unroll
         for (int r = 0; r < TR; ++r) {
             const float4 av = *reinterpret_cast<const float4*>(&As[r][tx * 4]);
@@ -61,8 +66,13 @@ __global__ void __launch_bounds__(NT) k_simt_gemm(SimtArgs a) {
             #pragma unroll
             for (int p = 0; p < 4; ++p)
                 #pragma unroll
-                for (int q = 0; q < 4; ++q) acc[p][q] = fmaf(ar[p], br[q], acc[p][q]);
+                for (int q = 0; q < 4; ++q) part[p][q] = fmaf(ar[p], br[q], part[p][q]);
         }
+        // two-level summation: 16-term partial sums, then one add into the running total
+        #pragma unroll
+        for (int p2 = 0; p2 < 4; ++p2)
+            #pragma unroll
+            for (int q2 = 0; q2 < 4; ++q2) acc[p2][q2] += part[p2][q2];
         __syncthreads();
     }
 

@@ -14,9 +14,11 @@ def fro_rel(a, ref):
     return float(np.linalg.norm(a - ref) / np.linalg.norm(ref))
 
 
-def survivors(W):
-    """indices of components (columns of W) that have not collapsed to zero"""
-    return sorted(np.nonzero(np.abs(W).sum(axis=0) > 1e-20)[0].tolist())
+def survivors(W, rel=1e-12):
+    """indices of components (columns of W) that have not collapsed: column mass above rel * the largest.
+    (The reference's golden holds exact zeros there; its build on B200 leaves denormal-scale residue.)"""
+    mass = np.abs(np.asarray(W, dtype=np.float64)).sum(axis=0)
+    return sorted(np.nonzero(mass > rel * mass.max())[0].tolist())
 
 
 def rand_problem(M, N, K, seed):
