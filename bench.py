@@ -82,10 +82,8 @@ class ClockSampler:
 
 
 def shard(N, rank, world):
-    """contiguous column blocks, multiples of 256 (the GEMM tile) except the last"""
-    per = -(-N // world); per = -(-per // 256) * 256
-    lo = min(N, rank * per); hi = min(N, lo + per)
-    return lo, hi - lo
+    from nmf_gpu_b200.sharding import column_shard
+    return column_shard(N, rank, world)
 
 
 def cpu_baseline(M, N, K, seed, target_s=12.0):

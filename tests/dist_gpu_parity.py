@@ -1,0 +1,63 @@
+"""Multi-GPU parity (run under torchrun on N GPUs): the column-sharded run must reproduce the
+single-GPU run of the same problem (differences come only from reduction order).
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tests/dist_gpu_parity.py
+Prints one PARITY line on rank 0 and exits non-zero on failure."""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import nmf_gpu_b200.api as api
+from nmf_gpu_b200.sharding import column_shard
+from util import max_rel, rand_problem
+
+
+def main():
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    M, N, K, iters = 1024, 4096 + 300, 96, 30
+    W, H, X = rand_problem(M, N, K, seed=11)
+    out = {}
+    for mode in ("exact", "refcompat"):
+        opt = api.options(semantics=mode, device=local)
+        lo, n = column_shard(N, rank, world)
+        s = api.Session(M, n, K, n_offset=lo, n_global=N, opt=opt)
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid = torch.frombuffer(bytearray(api.nccl_unique_id()), dtype=torch.uint8).cuda()
+        dist.broadcast(uid, 0)
+        s.join(rank, world, uid.cpu().numpy().tobytes())
+        s.upload(W, H[:, lo:lo + n], X[:, lo:lo + n])
+        res = s.run(1e-9, iters)                      # thresh > 0 exercises the allreduced cost too
+        Wd, Hd = s.download()
+        cost = s.cost()
+        s.close()
+        # gather the H shards on every rank
+        Hfull = torch.zeros((N, K), dtype=torch.float32, device="cuda")
+        Hfull[lo:lo + n] = torch.from_numpy(np.ascontiguousarray(Hd.T)).cuda()
+        dist.all_reduce(Hfull)
+        Hm = Hfull.cpu().numpy().T
+        if rank == 0:
+            W1, H1 = W.copy(order="F"), H.copy(order="F")
+            r1 = api.update_div(W1, H1, X, 1e-9, iters, opt=opt)
+            out[mode] = dict(W=max_rel(Wd, W1), H=max_rel(Hm, H1), cost_rel=abs(cost - r1.cost) / abs(r1.cost),
+                             iters=(res.iterations, r1.iterations))
+    ok = True
+    if rank == 0:
+        print("PARITY " + json.dumps(dict(world=world, **out)), flush=True)
+        ok = all(v["W"] < 2e-5 and v["H"] < 2e-5 and v["cost_rel"] < 1e-5 and v["iters"][0] == v["iters"][1]
+                 for k, v in out.items() if k == "exact")
+        ok &= out["refcompat"]["cost_rel"] < 1e-5
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()
