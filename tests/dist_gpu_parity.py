@@ -45,9 +45,12 @@ def main():
         dist.all_reduce(Hfull)
         Hm = Hfull.cpu().numpy().T
         if rank == 0:
-            W1, H1 = W.copy(order="F"), H.copy(order="F")
-            r1 = api.update_div(W1, H1, X, 1e-9, iters, opt=opt)
-            out[mode] = dict(W=max_rel(Wd, W1), H=max_rel(Hm, H1), cost_rel=abs(cost - r1.cost) / abs(r1.cost),
+            with api.Session(M, N, K, opt=opt) as s1:             # the same problem on one GPU
+                s1.upload(W, H, X)
+                r1 = s1.run(1e-9, iters)
+                W1, H1 = s1.download()
+                cost1 = s1.cost()
+            out[mode] = dict(W=max_rel(Wd, W1), H=max_rel(Hm, H1), cost_rel=abs(cost - cost1) / abs(cost1),
                              iters=(res.iterations, r1.iterations))
     ok = True
     if rank == 0:
