@@ -50,12 +50,16 @@ inline int ref_pad32(int v) { return (v != 1 && v % 32 != 0) ? v + (32 - v % 32)
 struct Dims {
     int M = 0, N = 0, K = 0;
     int Mv = 0, Nv = 0, Kv = 0;
+    int Nva = 0;             // columns ALLOCATED for X, Y, H (Nv rounded up to the 256-column GEMM tile, zero fill):
+                             // lets the fused epilogues store whole tiles without per-element column predicates
     long long n_offset = 0, n_global = 0;
     int refcompat = 0;
     int w_divide = 1;        // 0 iff refcompat and rows_padded(W) > 1024 (cuda/matrix.cu:212-217)
     size_t szW() const { return (size_t)Mv * Kv; }
     size_t szH() const { return (size_t)Kv * Nv; }
     size_t szX() const { return (size_t)Mv * Nv; }
+    size_t szHa() const { return (size_t)Kv * Nva; }
+    size_t szXa() const { return (size_t)Mv * Nva; }
 };
 
 Dims make_dims(int M, int n_local, int K, long long n_offset, long long n_global, int semantics);

@@ -37,6 +37,7 @@ Dims make_dims(int M, int n_local, int K, long long n_offset, long long n_global
         d.Mv = round_up(M, 32); d.Kv = round_up(K, 32); d.Nv = n_local;
         d.w_divide = 1;
     }
+    d.Nva = round_up(d.Nv, 256);
     return d;
 }
 
@@ -80,10 +81,10 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
         s->d = make_dims(M, n_local, K, n_offset, n_global, opt.semantics);
         const Dims& d = s->d;
         CUDA_CHECK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-        s->W = dalloc<float>(d.szW()); s->H = dalloc<float>(d.szH()); s->X = dalloc<float>(d.szX());
+        s->W = dalloc<float>(d.szW()); s->H = dalloc<float>(d.szHa()); s->X = dalloc<float>(d.szXa());
         CUDA_CHECK(cudaMemsetAsync(s->W, 0, d.szW() * 4, s->stream));
-        CUDA_CHECK(cudaMemsetAsync(s->H, 0, d.szH() * 4, s->stream));
-        CUDA_CHECK(cudaMemsetAsync(s->X, 0, d.szX() * 4, s->stream));
+        CUDA_CHECK(cudaMemsetAsync(s->H, 0, d.szHa() * 4, s->stream));
+        CUDA_CHECK(cudaMemsetAsync(s->X, 0, d.szXa() * 4, s->stream));
         s->sumW = dalloc<float>(d.Kv);
         s->packed = dalloc<float>(d.szW() + d.Kv);
         s->sumH = s->packed + d.szW();
@@ -91,13 +92,13 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
         s->cost_dev = dalloc<double>(1);
         CUDA_CHECK(cudaMallocHost((void**)&s->cost_host, sizeof(double)));
         if (opt.engine == NMF_ENGINE_SIMT) {
-            s->Y = dalloc<float>(d.szX());
+            s->Y = dalloc<float>(d.szXa());
             s->n_cost_partials = simt_cost_partial_count(d);
             s->nsplit = 1;
         } else {
-            s->Yhi = dalloc<float>(d.szX()); s->Ylo = dalloc<float>(d.szX());
+            s->Yhi = dalloc<float>(d.szXa()); s->Ylo = dalloc<float>(d.szXa());
             s->Whi = dalloc<float>(d.szW()); s->Wlo = dalloc<float>(d.szW());
-            s->Hhi = dalloc<float>(d.szH()); s->Hlo = dalloc<float>(d.szH());
+            s->Hhi = dalloc<float>(d.szHa()); s->Hlo = dalloc<float>(d.szHa());
             s->n_cost_partials = umma::cost_partial_count(d);
             s->nsplit = umma::numer_splits(d);
             if (s->nsplit > 1) s->Psplit = dalloc<float>((size_t)s->nsplit * d.szW());
