@@ -36,10 +36,13 @@ def oracle():
 # ---------------------------------------------------------------------------------------------
 # kernel level
 # ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("pair", [1, 0])
 @pytest.mark.parametrize("which", [0, 1, 2])
-@pytest.mark.parametrize("shape", [(128, 256, 64), (160, 100, 96), (384, 520, 160), (32, 4, 32)])
-def test_umma_raw_gemm_3xtf32(api, which, shape):
-    """the tensor-core contraction itself, all three operand-major combinations, ragged tiles"""
+@pytest.mark.parametrize("shape", [(128, 256, 64), (160, 100, 96), (384, 520, 160), (32, 4, 32), (640, 1100, 288)])
+def test_umma_raw_gemm_3xtf32(api, which, shape, pair, monkeypatch):
+    """the tensor-core contraction itself, all three operand-major combinations, ragged tiles;
+    pair=1: CTA pairs (cta_group::2, 256-row tiles) wherever the output has > 128 rows, pair=0: one-CTA tiles"""
+    monkeypatch.setenv("NMF_UMMA_PAIR", str(pair))
     M, N, K = shape
     rng = np.random.RandomState(which * 7 + M)
     sa, sb = {0: ((M, K), (K, N)), 1: ((M, K), (M, N)), 2: ((M, N), (K, N))}[which]
@@ -48,7 +51,9 @@ def test_umma_raw_gemm_3xtf32(api, which, shape):
     C = api.dbg_gemm(which, A, B, M, N, K, passes=3)
     A64, B64 = A.astype(np.float64), B.astype(np.float64)
     ref = {0: lambda: A64 @ B64, 1: lambda: A64.T @ B64, 2: lambda: A64 @ B64.T}[which]()
-    assert np.abs(C - ref).max() / np.abs(ref).max() < 2e-6      # fp32-class accuracy
+    # fp32-class accuracy; geometry 0 accumulates the whole reduction in TMEM, whose truncating adds
+    # leave a one-sided error that grows with the reduction length
+    assert np.abs(C - ref).max() / np.abs(ref).max() < 2e-6 * max(1.0, K / 160.0)
     C1 = api.dbg_gemm(which, A, B, M, N, K, passes=1)
     e1 = np.abs(C1 - ref).max() / np.abs(ref).max()
     assert 1e-6 < e1 < 5e-3                                        # single-pass TF32 is visibly coarser
