@@ -133,7 +133,10 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
     uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank)); return r;
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" :: "r"(cluster_addr) : "memory");
+    // default semantics (.release.cta): a cluster-scope release would drain every earlier global store
+    // of the warp first (ERRBAR + membar stall, 8 % of the epilogue's samples); the TMEM reads this
+    // arrive publishes are already complete (tcgen05.wait::ld + tcgen05.fence::before_thread_sync)
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" :: "r"(cluster_addr) : "memory");
 }
 // L2 eviction-priority policies (createpolicy): 1 = evict_first (streams), 2 = evict_last (reused operands)
 __device__ __forceinline__ uint64_t l2_policy(int kind) {
