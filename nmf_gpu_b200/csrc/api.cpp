@@ -222,13 +222,7 @@ int nmf_dbg_quotient(const float* W, const float* H, const float* X, float* Y, d
             iteration_head(s, cost != nullptr, nullptr);
             const Dims& d = s.d;
             std::vector<float> a((size_t)d.Mv * d.Nv), b;
-            if (s.opt.engine == NMF_ENGINE_SIMT) {
-                CUDA_CHECK(cudaMemcpyAsync(a.data(), s.Y, a.size() * 4, cudaMemcpyDeviceToHost, s.stream));
-            } else {   // Y = hi + lo exactly
-                b.resize(a.size());
-                CUDA_CHECK(cudaMemcpyAsync(a.data(), s.Yhi, a.size() * 4, cudaMemcpyDeviceToHost, s.stream));
-                CUDA_CHECK(cudaMemcpyAsync(b.data(), s.Ylo, a.size() * 4, cudaMemcpyDeviceToHost, s.stream));
-            }
+            CUDA_CHECK(cudaMemcpyAsync(a.data(), s.Y, a.size() * 4, cudaMemcpyDeviceToHost, s.stream));
             if (cost) CUDA_CHECK(cudaMemcpyAsync(s.cost_host, s.cost_dev, 8, cudaMemcpyDeviceToHost, s.stream));
             CUDA_CHECK(cudaStreamSynchronize(s.stream));
             if (cost) *cost = *s.cost_host;

@@ -96,7 +96,7 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
             s->n_cost_partials = simt_cost_partial_count(d);
             s->nsplit = 1;
         } else {
-            s->Yhi = dalloc<float>(d.szXa()); s->Ylo = dalloc<float>(d.szXa());
+            s->Y = dalloc<float>(d.szXa());     // stored once as fp32; the GEMMs that consume it split it in the SM
             s->Whi = dalloc<float>(d.szW()); s->Wlo = dalloc<float>(d.szW());
             s->Hhi = dalloc<float>(d.szHa()); s->Hlo = dalloc<float>(d.szHa());
             s->n_cost_partials = umma::cost_partial_count(d);
