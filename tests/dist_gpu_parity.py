@@ -22,7 +22,7 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     rank, world = dist.get_rank(), dist.get_world_size()
-    M, N, K, iters = 1024, 4096 + 300, 96, 30
+    M, N, K, iters = 1024, max(4096, 1024 * world) + 300, 96, 30      # every rank owns columns (shards are 128-column blocks)
     W, H, X = rand_problem(M, N, K, seed=11)
     out = {}
     for mode in ("exact", "refcompat"):
