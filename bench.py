@@ -31,7 +31,10 @@ sys.path.insert(0, ROOT)
 WORKLOADS = {                     # name: (M, N, K, seed, description)
     "c4": (16384, 262144, 256, 4, "C4 large synthetic NMF 16384x262144 K=256"),
     "c5": (8192, 131072, 256, 5, "C5 8192x131072 K=256"),
+    "c3": (2049, 1000000, 128, 3, "C3 spectrogram NMF 2049x1000000 K=128"),
     "c3s": (2049, 262144, 128, 3, "C3-shape 2049x262144 K=128"),
+    "c5k64": (8192, 131072, 64, 5, "C5 8192x131072 K=64"),
+    "c5k512": (8192, 131072, 512, 5, "C5 8192x131072 K=512"),
     "c2": (513, 20000, 40, 1, "C2 audio spectrogram 513x20000 K=40"),
     "c1": (4096, 350, 128, 0, "C1 bundled shape 4096x350 K=128"),
     "mid": (8192, 32768, 256, 7, "mid 8192x32768 K=256 (profiling size)"),

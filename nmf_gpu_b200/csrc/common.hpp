@@ -94,6 +94,9 @@ void launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nspli
 
 // out[e] = sum_s P[s][e] in split order (multi-GPU: fold the local splits before the allreduce).
 void launch_fold_splits(const float* P, int nsplit, size_t split_stride, float* out, size_t n, cudaStream_t st);
+// H <- H .* ((sum of the nsplit partial W'*Y) ./ max(sumW,EPS)), plus the TF32 pair of the new H
+void launch_update_h(float* H, float* Hhi, float* Hlo, const float* P, int nsplit, size_t split_stride,
+                     const float* sumW, const Dims& d, cudaStream_t st);
 
 // cost = sum of `n` double partials (ordered).
 void launch_sum_partials(const double* partials, int n, double* out, cudaStream_t st);

@@ -158,6 +158,36 @@ __global__ void __launch_bounds__(256) k_update_w(float* __restrict__ W, float* 
     }
 }
 
+// H update from split partial sums of W'*Y (small problems: the H GEMM is split over the rows of W so
+// that it fills the SMs): H <- H .* ((sum_s P[s]) ./ max(sumW,EPS)), ordered sum, emits the TF32 pair.
+// One thread per 4 consecutive k of one column (float4; Kv is a multiple of 32).
+__global__ void __launch_bounds__(256) k_update_h(float* __restrict__ H, float* __restrict__ Hhi, float* __restrict__ Hlo,
+                                                  const float* __restrict__ P, int nsplit, size_t split_stride,
+                                                  const float* __restrict__ sumW, int Kv, size_t total4) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t e = i * 4;
+        const int k = (int)(e % (size_t)Kv);
+        float4 acc = *reinterpret_cast<const float4*>(P + e);
+        for (int s = 1; s < nsplit; ++s) {
+            const float4 p = *reinterpret_cast<const float4*>(P + (size_t)s * split_stride + e);
+            acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+        }
+        const float4 sw = *reinterpret_cast<const float4*>(sumW + k);
+        acc.x = acc.x / clampE(sw.x); acc.y = acc.y / clampE(sw.y);      // col_div, cuda/matrix.cu:244-250
+        acc.z = acc.z / clampE(sw.z); acc.w = acc.w / clampE(sw.w);
+        float4 h = *reinterpret_cast<float4*>(H + e);
+        h.x *= acc.x; h.y *= acc.y; h.z *= acc.z; h.w *= acc.w;          // vec_mul, cuda/matrix.cu:174-180
+        *reinterpret_cast<float4*>(H + e) = h;
+        if (Hhi != nullptr) {
+            float4 hi, lo;
+            tf32_split(h.x, hi.x, lo.x); tf32_split(h.y, hi.y, lo.y);
+            tf32_split(h.z, hi.z, lo.z); tf32_split(h.w, hi.w, lo.w);
+            *reinterpret_cast<float4*>(Hhi + e) = hi;
+            *reinterpret_cast<float4*>(Hlo + e) = lo;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) k_fold_splits(const float* __restrict__ P, int nsplit, size_t split_stride,
                                                      float* __restrict__ out, size_t n4) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
@@ -233,6 +263,13 @@ void launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nspli
                      const float* sumH, const Dims& d, cudaStream_t st) {
     k_update_w<<<grid_for(d.szW() / 4, 256), 256, 0, st>>>(W, Whi, Wlo, P, nsplit, split_stride, sumH,
                                                            d.Mv, d.Kv, d.w_divide);
+    CUDA_CHECK_LAUNCH();
+}
+
+void launch_update_h(float* H, float* Hhi, float* Hlo, const float* P, int nsplit, size_t split_stride,
+                     const float* sumW, const Dims& d, cudaStream_t st) {
+    const size_t total4 = (size_t)d.Kv * d.Nv / 4;
+    k_update_h<<<grid_for(total4, 256), 256, 0, st>>>(H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4);
     CUDA_CHECK_LAUNCH();
 }
 

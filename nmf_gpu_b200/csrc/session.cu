@@ -59,7 +59,7 @@ nmf_session_impl::~nmf_session_impl() {
     if (g_rest) cudaGraphExecDestroy(g_rest);
     if (plan) umma::plan_destroy(plan);
     if (nccl) nccl_destroy(nccl);
-    float* fl[] = {W, H, X, Y, Yhi, Ylo, Whi, Wlo, Hhi, Hlo, sumW, packed, Psplit, rowsum_partials};
+    float* fl[] = {W, H, X, Y, Whi, Wlo, Hhi, Hlo, sumW, packed, Psplit, Hpart, rowsum_partials};
     for (float* p : fl) if (p) cudaFree(p);
     if (cost_partials) cudaFree(cost_partials);
     if (cost_dev) cudaFree(cost_dev);
@@ -102,6 +102,8 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
             s->n_cost_partials = umma::cost_partial_count(d);
             s->nsplit = umma::numer_splits(d);
             if (s->nsplit > 1) s->Psplit = dalloc<float>((size_t)s->nsplit * d.szW());
+            s->hsplit = umma::updh_splits(d);
+            if (s->hsplit > 1) s->Hpart = dalloc<float>((size_t)s->hsplit * d.szHa());
             s->plan = umma::plan_create(*s);
         }
         s->cost_partials = dalloc<double>(s->n_cost_partials > 0 ? s->n_cost_partials : 1);
@@ -222,7 +224,7 @@ void iteration_rest(nmf_session_impl& s, PhaseTimer* pt) {
     PHASE(pt, PH_GEMM2, {
         if (s.opt.engine == NMF_ENGINE_SIMT) simt_update_h(s.W, s.Y, s.sumW, s.H, d, s.stream);
         else umma::update_h(s);
-        count_launches(s, 1);
+        count_launches(s, (s.opt.engine == NMF_ENGINE_TCGEN05 && s.hsplit > 1) ? 2 : 1);   // split: GEMM partials + fold/update kernel
     });
     // sum rows of H (nmf.cu:164) into the packed buffer's tail
     PHASE(pt, PH_SUMS, { launch_rowsum(s.H, s.rowsum_partials, s.sumH, d, s.stream); count_launches(s, 2); });

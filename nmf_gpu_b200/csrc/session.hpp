@@ -17,12 +17,13 @@ struct nmf_session_impl {
     // fp32 masters (column-major, ld = Mv / Kv)
     float *W = nullptr, *H = nullptr, *X = nullptr;
     // quotient Y = X ./ max(WH,EPS): SIMT engine keeps one fp32 copy, tcgen05 engine the TF32 split
-    float *Y = nullptr, *Yhi = nullptr, *Ylo = nullptr;
+    float *Y = nullptr;                           // quotient X ./ max(W*H,EPS), stored once as fp32
     // TF32 splits of the small operands (tcgen05 engine)
     float *Whi = nullptr, *Wlo = nullptr, *Hhi = nullptr, *Hlo = nullptr;
     // sums and the packed allreduce buffer [ numerator P (Mv*Kv) | sumH (Kv) ]
     float *sumW = nullptr, *packed = nullptr, *sumH = nullptr /* = packed + Mv*Kv */;
     float *Psplit = nullptr; int nsplit = 1;      // split-N partial numerators (tcgen05 engine)
+    float *Hpart = nullptr; int hsplit = 1;       // split-M partial W'*Y of the H update (small problems only)
     float *rowsum_partials = nullptr;
     double *cost_partials = nullptr; int n_cost_partials = 0;
     double *cost_dev = nullptr, *cost_host = nullptr /* pinned */;
@@ -62,6 +63,7 @@ Plan* plan_create(nmf_session_impl& s);
 void  plan_destroy(Plan* p);
 int   cost_partial_count(const Dims& d);
 int   numer_splits(const Dims& d);
+int   updh_splits(const Dims& d);
 void  quotient(nmf_session_impl& s, bool with_cost);
 void  update_h(nmf_session_impl& s);
 void  numer(nmf_session_impl& s);
