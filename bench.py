@@ -204,8 +204,14 @@ def main():
     peak3 = pk["bf16_sustained"] / 2.0 / 3.0                  # TF32 dense = bf16/2; 3 MMAs per product
     # dominant kernel = k_umma<QUOT> (W*H with the fused clamp/divide), 2*M*n_loc*K algorithmic flop per launch
     ach = 2.0 * M * n_loc * K / (quot_ms * 1e-3) / 1e12 if quot_ms > 0 else 0.0
+    traffic = None
+    try:   # DRAM bytes per launch of the same kernel from the committed ncu --set full capture (profiles/)
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get(str(world))
+    except (OSError, ValueError):
+        pass
     roofline = {"bound": "tensor", "kernel": "k_umma<QUOT> (W*H GEMM + fused X./max(.,EPS), 3xTF32)",
-                "achieved": ach, "peak": peak3, "unit": "TFLOP/s", "frac": ach / peak3, "traffic": None,
+                "achieved": ach, "peak": peak3, "unit": "TFLOP/s", "frac": ach / peak3, "traffic": traffic,
+                "algorithmic_hbm_bytes": 8.0 * M * n_loc + 8.0 * K * (M + n_loc),   # X read + Y written once, W and H (hi, lo) read
                 "peak_note": f"{pk['source']}: bf16 sustained {pk['bf16_sustained']:.0f} TF/s / 2 (TF32) / 3 (3xTF32 passes)",
                 "launch_ms": quot_ms, "other_gemm_launch_ms": gemm2_ms,
                 "whole_iteration_frac": (flop_iter / world / (ms_per_step * 1e-3) / 1e12) / peak3,
