@@ -91,7 +91,7 @@ def test_sums(api, engine, mode):
 
 @pytest.mark.parametrize("engine", ENGINES)
 @pytest.mark.parametrize("mode", ["exact", "refcompat"])
-@pytest.mark.parametrize("shape", [(256, 512, 64), (130, 70, 40), (1100, 90, 33)])
+@pytest.mark.parametrize("shape", [(256, 512, 64), (130, 70, 40), (1100, 90, 33), (300, 700, 160), (600, 1300, 256)])
 def test_half_steps(api, oracle, engine, mode, shape):
     M, N, K = shape
     W, H, X = rand_problem(M, N, K, seed=K)
@@ -100,6 +100,42 @@ def test_half_steps(api, oracle, engine, mode, shape):
     assert max_rel(H1, oracle.h_step(W, H, X, mode, acc64=True)) < 2e-5
     W1 = api.dbg_w_step(W, H, X, opt)
     assert max_rel(W1, oracle.w_step(W, H, X, mode, acc64=True)) < 2e-5
+
+
+@pytest.mark.parametrize("hsplit", ["1", "3", ""])
+@pytest.mark.parametrize("pair", ["1", "0"])
+def test_h_step_tile_modes(api, oracle, hsplit, pair, monkeypatch):
+    """the H update through every tiling of the tcgen05 engine: CTA pairs (K > 128) or single CTAs, the
+    fused epilogue (hsplit 1), a forced 3-way split of the reduction over the rows of W (partials
+    folded by k_update_h) and the automatic choice; wide enough (38+ column tiles) that the automatic
+    choice keeps the fused epilogue"""
+    monkeypatch.setenv("NMF_UMMA_PAIR", pair)
+    if hsplit:
+        monkeypatch.setenv("NMF_UMMA_HSPLIT", hsplit)
+    M, N, K = 300, 10000, 160
+    W, H, X = rand_problem(M, N, K, seed=21)
+    H1 = api.dbg_h_step(W, H, X, api.options())
+    assert max_rel(H1, oracle.h_step(W, H, X, "exact", acc64=True)) < 2e-5
+    W1 = api.dbg_w_step(W, H, X, api.options())
+    assert max_rel(W1, oracle.w_step(W, H, X, "exact", acc64=True)) < 2e-5
+
+
+@pytest.mark.parametrize("chunk", [1, 4, 16])
+def test_chunk_period_bounds_truncation_bias(api, chunk, monkeypatch):
+    """tcgen05.mma truncates its fp32 accumulator, so an all-positive reduction comes out low by an
+    amount proportional to the number of 32-deep blocks accumulated in TMEM between two
+    round-to-nearest promotions (`chunk`).  Measured on B200 (profiles/r1_bias_probe.txt):
+    -1.2e-7, -4e-7, -1e-6, -2.3e-6, -4.9e-6 relative for chunk 1, 2, 4, 8, 16, independent of the
+    reduction length (16384 here would be ~1e-4 unchunked).  The default (4) must stay ~1e-6."""
+    monkeypatch.setenv("NMF_UMMA_CHUNK", str(chunk))
+    M, N, K = 8192, 96, 64
+    rng = np.random.RandomState(3)
+    A = np.asfortranarray(rng.rand(M, K).astype(np.float32))
+    B = np.asfortranarray(rng.rand(M, N).astype(np.float32))
+    C = api.dbg_gemm(1, A, B, M, N, K, passes=3)                  # W' * Y, reduction over M = 8192
+    ref = A.astype(np.float64).T @ B.astype(np.float64)
+    err = (C - ref) / ref
+    assert abs(err.mean()) < 4e-7 * chunk and np.abs(err).max() < 1e-6 + 4e-7 * chunk
 
 
 # ---------------------------------------------------------------------------------------------
