@@ -101,7 +101,7 @@ def lib():
     """Loads (building if needed) libnmf_b200.so; raises if it cannot — no fallback."""
     global _lib
     if _lib is None:
-        path = _build.build()
+        path = os.environ.get("NMF_B200_LIB") or _build.build()      # override: A/B builds of the same ABI (development)
         L = ctypes.CDLL(path)
         for name, (res, args) in _SIGNATURES.items():
             fn = getattr(L, name)          # AttributeError if the library misses a declared symbol
