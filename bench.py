@@ -216,7 +216,8 @@ def main():
                 "launch_ms": quot_ms, "other_gemm_launch_ms": gemm2_ms,
                 "whole_iteration_frac": (flop_iter / world / (ms_per_step * 1e-3) / 1e12) / peak3,
                 "phase_seconds_3_iterations": [float(v) for v in t]}
-    sess.close()
+    if world == 1:
+        sess.close()      # N > 1: kept until the e2e run has shared its communicator (a process creates NCCL once)
 
     # ---- e2e: host buffers, H2D and D2H inside the timed region --------------------------------
     e2e = None
@@ -232,7 +233,7 @@ def main():
             r2 = api.update_div(Wn, Hn, Xn, 0.0, args.steps, opt=opt)     # the reference-facing call
         else:
             s2 = api.Session(M, n_loc, K, n_offset=n_off, n_global=N, opt=opt)
-            join(s2)
+            s2.share_comm(sess)                                            # the process-wide communicator
             s2.upload(Wn, Hn, Xn); r2 = s2.run(0.0, args.steps); s2.download(); s2.close()
         torch.cuda.synchronize()
         dt = max_over_ranks(time.perf_counter() - t0)
@@ -243,6 +244,8 @@ def main():
                "seconds": dt, "call": "update_div(W,H,X,0,steps)" if world == 1 else "Session.upload/run/download per rank",
                "loop_device_ms": r2.device_ms}
         del Xh, Wh, Hh
+    if world > 1:
+        sess.close()
 
     if rank == 0:
         line = {"metric": "nmf_iterations_per_s", "value": value, "unit": "iterations/s", "n_gpus": world,

@@ -131,6 +131,9 @@ int nmf_session_fill_uniform(nmf_session *s, unsigned long long seed, int which)
  * nmf_nccl_unique_id() on rank 0 and broadcast by the host (torch.distributed, MPI, a file...). */
 int nmf_nccl_unique_id(void *id128);
 int nmf_session_join(nmf_session *s, int rank, int nranks, const void *id128);
+/* A further session of the same process reuses src's communicator (ncclCommInitRank costs seconds; a
+ * process makes it once).  The communicator lives until the last session that holds it is destroyed. */
+int nmf_session_share_comm(nmf_session *dst, nmf_session *src);
 
 /* Runs the iteration (the body of update_div) on the resident data. */
 int nmf_session_run(nmf_session *s, float CONVERGE_THRESH, int max_iter, double t[10], int verbose,

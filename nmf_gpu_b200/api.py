@@ -77,6 +77,7 @@ _SIGNATURES = {
     "nmf_session_fill_uniform": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_ulonglong, ctypes.c_int]),
     "nmf_nccl_unique_id": (ctypes.c_int, [ctypes.c_void_p]),
     "nmf_session_join": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
+    "nmf_session_share_comm": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
     "nmf_session_run": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_float, ctypes.c_int, _f64p, ctypes.c_int,
                                        ctypes.POINTER(nmf_result)]),
     "nmf_session_cost": (ctypes.c_int, [ctypes.c_void_p, _f64p]),
@@ -216,6 +217,10 @@ class Session:
     def join(self, rank, nranks, unique_id):
         buf = ctypes.create_string_buffer(bytes(unique_id), 128)
         _check(lib().nmf_session_join(self._h, int(rank), int(nranks), buf))
+
+    def share_comm(self, other):
+        """reuse `other`'s NCCL communicator (same process, same device) instead of a new ncclCommInitRank"""
+        _check(lib().nmf_session_share_comm(self._h, other._h))
 
     def run(self, CONVERGE_THRESH=0.0, max_iter=1, t=None, verbose=0):
         res = nmf_result()

@@ -191,6 +191,10 @@ int nmf_session_download(nmf_session* s, float* W, float* H) {
 int nmf_session_fill_uniform(nmf_session* s, unsigned long long seed, int which) {
     return guarded([&] { NMF_CHECK(s, "NULL session"); session_fill_uniform(*s, seed, which); });
 }
+int nmf_session_share_comm(nmf_session* dst, nmf_session* src) {
+    return guarded([&] { NMF_CHECK(dst && src, "NULL session"); nccl_share(*dst, *src); });
+}
+
 int nmf_nccl_unique_id(void* id128) { return guarded([&] { nccl_unique_id(id128); }); }
 int nmf_session_join(nmf_session* s, int rank, int nranks, const void* id128) {
     return guarded([&] { NMF_CHECK(s, "NULL session"); nccl_join(*s, rank, nranks, id128); });

@@ -43,7 +43,7 @@ void check(int r, const char* what) {
 }
 }  // namespace
 
-struct Nccl { ncclComm_t comm = nullptr; };
+struct Nccl { ncclComm_t comm = nullptr; int refs = 1; };   // shared by the sessions of one process (nccl_share)
 
 int nccl_unique_id(void* id128) {
     ncclUniqueId id;
@@ -75,8 +75,19 @@ void nccl_allreduce_f64(nmf_session_impl& s, double* buf, size_t n) {
     check(api().AllReduce(buf, buf, n, ncclFloat64, ncclSum, s.nccl->comm, s.stream), "ncclAllReduce(f64)");
 }
 
+// A second session of the same process (same rank, same device) reuses the communicator of `src`:
+// ncclCommInitRank costs seconds, a process makes it once.
+void nccl_share(nmf_session_impl& dst, nmf_session_impl& src) {
+    NMF_CHECK(dst.nccl == nullptr && dst.g_full == nullptr, "share the communicator before the first run, once");
+    NMF_CHECK(dst.device == src.device, "sessions that share a communicator must be on the same device");
+    if (src.nccl == nullptr) { dst.rank = 0; dst.nranks = 1; return; }
+    src.nccl->refs += 1;
+    dst.nccl = src.nccl; dst.rank = src.rank; dst.nranks = src.nranks;
+}
+
 void nccl_destroy(Nccl* n) {
     if (!n) return;
+    if (--n->refs > 0) return;
     if (n->comm) api().CommDestroy(n->comm);
     delete n;
 }

@@ -56,6 +56,7 @@ void nccl_join(nmf_session_impl& s, int rank, int nranks, const void* id128);
 void nccl_allreduce_f32(nmf_session_impl& s, float* buf, size_t n);
 void nccl_allreduce_f64(nmf_session_impl& s, double* buf, size_t n);
 void nccl_destroy(Nccl* n);
+void nccl_share(nmf_session_impl& dst, nmf_session_impl& src);
 
 namespace umma {
 // tcgen05 engine (kernels_umma.cu)

@@ -38,6 +38,12 @@ def main():
         res = s.run(1e-9, iters)                      # thresh > 0 exercises the allreduced cost too
         Wd, Hd = s.download()
         cost = s.cost()
+        # a second session of this process on the shared communicator reproduces the run bit for bit
+        s2 = api.Session(M, n, K, n_offset=lo, n_global=N, opt=opt)
+        s2.share_comm(s)
+        s2.upload(W, H[:, lo:lo + n], X[:, lo:lo + n]); s2.run(1e-9, iters)
+        W2, H2 = s2.download(); s2.close()
+        assert np.array_equal(W2, Wd) and np.array_equal(H2, Hd), "shared-communicator session differs"
         s.close()
         # gather the H shards on every rank
         Hfull = torch.zeros((N, K), dtype=torch.float32, device="cuda")
