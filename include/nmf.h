@@ -126,6 +126,9 @@ int nmf_session_download(nmf_session *s, float *W, float *H_local);
 /* Synthetic uniform(0,1) data generated on the device from a counter-based hash of the GLOBAL
  * (row, col) index, so any column sharding yields the same problem.  which: bit0 W, bit1 H, bit2 X */
 int nmf_session_fill_uniform(nmf_session *s, unsigned long long seed, int which);
+/* X <- (A*B) .* (1 + noise*(2u-1)), A (M x rank), B (rank x N), u uniform(0,1) from the same global-index
+ * hash: a planted low-rank target on which the convergence test is meaningful (BASELINE config C3). */
+int nmf_session_fill_planted(nmf_session *s, unsigned long long seed, int rank, float noise);
 
 /* Join an NCCL communicator (one process per GPU).  id = 128-byte ncclUniqueId obtained from
  * nmf_nccl_unique_id() on rank 0 and broadcast by the host (torch.distributed, MPI, a file...). */

@@ -78,6 +78,7 @@ _SIGNATURES = {
     "nmf_nccl_unique_id": (ctypes.c_int, [ctypes.c_void_p]),
     "nmf_session_join": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
     "nmf_session_share_comm": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
+    "nmf_session_fill_planted": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_ulonglong, ctypes.c_int, ctypes.c_float]),
     "nmf_session_run": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_float, ctypes.c_int, _f64p, ctypes.c_int,
                                        ctypes.POINTER(nmf_result)]),
     "nmf_session_cost": (ctypes.c_int, [ctypes.c_void_p, _f64p]),
@@ -213,6 +214,10 @@ class Session:
 
     def fill_uniform(self, seed, which=7):
         _check(lib().nmf_session_fill_uniform(self._h, int(seed), int(which)))
+
+    def fill_planted(self, seed, rank, noise=0.05):
+        """X <- planted rank-`rank` product with +-noise multiplicative uniform noise (W, H untouched)"""
+        _check(lib().nmf_session_fill_planted(self._h, int(seed), int(rank), float(noise)))
 
     def join(self, rank, nranks, unique_id):
         buf = ctypes.create_string_buffer(bytes(unique_id), 128)

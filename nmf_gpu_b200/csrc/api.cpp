@@ -14,6 +14,7 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
 void session_upload(nmf_session_impl& s, const float* W, const float* H, const float* X);
 void session_download(nmf_session_impl& s, float* W, float* H);
 void session_fill_uniform(nmf_session_impl& s, unsigned long long seed, int which);
+void session_fill_planted(nmf_session_impl& s, unsigned long long seed, int rank, float noise);
 void session_run(nmf_session_impl& s, float thresh, int max_iter, double t[10], int verbose, nmf_result* res);
 void session_cost(nmf_session_impl& s, double* cost);
 }  // namespace nmf
@@ -191,6 +192,10 @@ int nmf_session_download(nmf_session* s, float* W, float* H) {
 int nmf_session_fill_uniform(nmf_session* s, unsigned long long seed, int which) {
     return guarded([&] { NMF_CHECK(s, "NULL session"); session_fill_uniform(*s, seed, which); });
 }
+int nmf_session_fill_planted(nmf_session* s, unsigned long long seed, int rank, float noise) {
+    return guarded([&] { NMF_CHECK(s, "NULL session"); session_fill_planted(*s, seed, rank, noise); });
+}
+
 int nmf_session_share_comm(nmf_session* dst, nmf_session* src) {
     return guarded([&] { NMF_CHECK(dst && src, "NULL session"); nccl_share(*dst, *src); });
 }

@@ -72,6 +72,8 @@ void launch_clamp_eps(float* a, int rows, int cols, int ld, cudaStream_t st);
 // Fill rows [r0,r1) x cols [c0,c1) with value (used for the refcompat EPS padding).
 void launch_fill_region(float* a, int ld, int r0, int r1, int c0, int c1, float value, cudaStream_t st);
 // uniform(0,1) from a hash of (seed, tag, global row, global col); rows x cols, then clampE.
+void launch_fill_planted(float* x, int rows, int cols, int ld, long long col_offset, unsigned long long seed,
+                         int rank, float noise, cudaStream_t st);
 void launch_fill_uniform(float* a, int rows, int cols, int ld, long long col_offset,
                          unsigned long long seed, int tag, cudaStream_t st);
 // hi = x with the low 13 mantissa bits cleared (exactly representable in TF32), lo = x - hi (exact).

@@ -64,6 +64,30 @@ __global__ void k_fill_uniform(float* __restrict__ a, int rows, int cols, int ld
     }
 }
 
+// Planted low-rank target (BASELINE config C3): X[m,n] = (sum_k A[m,k] B[k,n]) * (1 + noise*(2u-1)) with
+// A, B, u uniform(0,1) drawn from the same counter-based hash of the GLOBAL indices (tags 11, 12, 13),
+// so any column sharding generates the same matrix.  One thread per element, rank `rank` dot product.
+__device__ __forceinline__ float hash_u01(unsigned long long seed, int tag, unsigned long long a, unsigned long long b) {
+    unsigned long long h = mix64(seed * 0x9E3779B97F4A7C15ull + (unsigned long long)tag);
+    h = mix64(h ^ (b * 0xD1B54A32D192ED03ull + a));
+    return (float)(h >> 40) * (1.0f / 16777216.0f);
+}
+
+__global__ void k_fill_planted(float* __restrict__ x, int rows, int cols, int ld, long long col_offset,
+                               unsigned long long seed, int rank, float noise) {
+    const size_t total = (size_t)rows * cols;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (size_t)gridDim.x * blockDim.x) {
+        const size_t c = i / rows, r = i - c * rows;
+        const unsigned long long gc = (unsigned long long)(col_offset + (long long)c);
+        float acc = 0.0f;
+        for (int k = 0; k < rank; ++k)
+            acc = fmaf(hash_u01(seed, 11, r, (unsigned long long)k), hash_u01(seed, 12, (unsigned long long)k, gc), acc);
+        const float u = hash_u01(seed, 13, r, gc);
+        x[c * (size_t)ld + r] = clampE(acc * (1.0f + noise * (2.0f * u - 1.0f)));
+    }
+}
+
 __global__ void k_split_tf32(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo, size_t n) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         float h, l;
@@ -234,6 +258,13 @@ void launch_fill_uniform(float* a, int rows, int cols, int ld, long long col_off
                          unsigned long long seed, int tag, cudaStream_t st) {
     if ((size_t)rows * cols == 0) return;
     k_fill_uniform<<<grid_for((size_t)rows * cols, 256), 256, 0, st>>>(a, rows, cols, ld, col_offset, seed, tag);
+    CUDA_CHECK_LAUNCH();
+}
+
+void launch_fill_planted(float* x, int rows, int cols, int ld, long long col_offset, unsigned long long seed,
+                         int rank, float noise, cudaStream_t st) {
+    if ((size_t)rows * cols == 0) return;
+    k_fill_planted<<<grid_for((size_t)rows * cols, 256), 256, 0, st>>>(x, rows, cols, ld, col_offset, seed, rank, noise);
     CUDA_CHECK_LAUNCH();
 }
 

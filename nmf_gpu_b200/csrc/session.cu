@@ -167,6 +167,17 @@ void session_fill_uniform(nmf_session_impl& s, unsigned long long seed, int whic
     CUDA_CHECK(cudaStreamSynchronize(s.stream));
 }
 
+// X <- planted rank-`rank` product with multiplicative uniform noise (BASELINE C3's input); W, H untouched
+void session_fill_planted(nmf_session_impl& s, unsigned long long seed, int rank, float noise) {
+    const Dims& d = s.d;
+    CUDA_CHECK(cudaSetDevice(s.device));
+    NMF_CHECK(rank >= 1, "planted rank must be positive");
+    CUDA_CHECK(cudaMemsetAsync(s.X, 0, d.szXa() * 4, s.stream));
+    launch_fill_planted(s.X, d.M, d.N, d.Mv, d.n_offset, seed, rank, noise, s.stream);
+    if (d.refcompat) launch_clamp_eps(s.X, d.Mv, d.Nv, d.Mv, s.stream);
+    CUDA_CHECK(cudaStreamSynchronize(s.stream));
+}
+
 // ---------------------------------------------------------------------------------------------
 // per-phase timing for t[10]: cudaEvent pairs around each phase, accumulated after a sync.
 // ---------------------------------------------------------------------------------------------

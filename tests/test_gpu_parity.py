@@ -224,6 +224,26 @@ def test_full_size_properties(api):
     assert np.array_equal(Hhalf, Hfull[:, N // 2:])
 
 
+def test_planted_target_converges_and_is_shard_independent(api):
+    """BASELINE C3's input family: a planted low-rank target.  The thresholded run stops before the cap
+    with a much smaller divergence, and the generator depends only on global indices."""
+    M, N, K = 513, 4096, 16
+    with api.Session(M, N, K) as s:
+        s.fill_uniform(3, which=3)
+        s.fill_planted(3, K, 0.05)
+        c0 = s.cost()
+        res = s.run(1e-3, 2000)
+        assert res.converged == 1 and 25 <= res.iterations < 2000 and res.iterations % 25 == 0
+        assert res.cost < 0.05 * c0
+    def cost_of(n_off, n_loc):
+        with api.Session(M, n_loc, K, n_offset=n_off, n_global=N) as t:
+            t.fill_uniform(3, which=3)
+            t.fill_planted(3, K, 0.05)
+            return t.cost()
+    full, left, right = cost_of(0, N), cost_of(0, N // 2), cost_of(N // 2, N // 2)
+    assert abs(full - (left + right)) <= 1e-6 * abs(full)          # the divergence is a sum over columns
+
+
 def test_shape_mismatch_raises(api):
     W, H, X = rand_problem(64, 64, 32, seed=1)
     with pytest.raises(api.NmfError):
