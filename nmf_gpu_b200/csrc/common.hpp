@@ -50,7 +50,7 @@ inline int ref_pad32(int v) { return (v != 1 && v % 32 != 0) ? v + (32 - v % 32)
 struct Dims {
     int M = 0, N = 0, K = 0;
     int Mv = 0, Nv = 0, Kv = 0;
-    int Nva = 0;             // columns ALLOCATED for X, Y, H (Nv rounded up to the 256-column GEMM tile, zero fill):
+    int Nva = 0;             // columns ALLOCATED for X, Y, H (Nv rounded up to 768 = lcm of the GEMM tile widths, zero fill):
                              // lets the fused epilogues store whole tiles without per-element column predicates
     long long n_offset = 0, n_global = 0;
     int refcompat = 0;

@@ -37,7 +37,7 @@ Dims make_dims(int M, int n_local, int K, long long n_offset, long long n_global
         d.Mv = round_up(M, 32); d.Kv = round_up(K, 32); d.Nv = n_local;
         d.w_divide = 1;
     }
-    d.Nva = round_up(d.Nv, 256);
+    d.Nva = round_up(d.Nv, 768);      // whole tiles of every width the engine uses (64, 128, 192, 256)
     return d;
 }
 
