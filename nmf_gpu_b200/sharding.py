@@ -5,12 +5,16 @@ import numpy as np
 
 
 def column_shard(N, rank, world, multiple=256):
-    """(first column, column count) of `rank`'s block.  Blocks are multiples of the GEMM tile width
-    (so only the last rank sees a ragged tile) and may be empty for tiny N."""
-    per = -(-N // world)
-    per = -(-per // multiple) * multiple
-    lo = min(N, rank * per)
-    return lo, min(N, lo + per) - lo
+    """(first column, column count) of `rank`'s block.  The ceil(N / multiple) tile-wide column blocks
+    are dealt out as evenly as possible (the first ranks get one more), so block boundaries fall on
+    GEMM tile boundaries, only the last non-empty rank sees a ragged tile, and a shard is empty only
+    when there are fewer blocks than ranks."""
+    nblocks = -(-N // multiple)
+    base, extra = divmod(nblocks, world)
+    first = rank * base + min(rank, extra)
+    count = base + (1 if rank < extra else 0)
+    lo = min(N, first * multiple)
+    return lo, min(N, (first + count) * multiple) - lo
 
 
 def packed_size(M, K):
