@@ -69,7 +69,10 @@ void destroy_matrix(matrix *A);
  *                     t[9] total wall time of the call
  *   verbose         : 1 prints the cost every 25 iterations
  * Semantics (exact | refcompat) and GPU selection come from the environment: NMF_SEMANTICS,
- * NMF_DEVICE, NMF_ENGINE; defaults: exact, device 0, tcgen05 engine. */
+ * NMF_DEVICE, NMF_ENGINE; defaults: exact, device 0, tcgen05 engine.
+ * NMF_NUM_GPUS=g (default 1) runs the call on g GPUs of this box from this one process — the GPU
+ * count is not part of the reference's signature: a host thread per GPU (devices NMF_DEVICE ..
+ * NMF_DEVICE+g-1), X and H sharded by columns, W replicated, one NCCL allreduce per iteration. */
 void update_div(matrix W, matrix H, matrix X, float CONVERGE_THRESH, int max_iter, double t[10],
                 int verbose);
 

@@ -1,6 +1,8 @@
 // api.cpp — the extern "C" boundary of libnmf_b200.so (include/nmf.h): the reference's host API
 // (read_matrix / write_matrix / update_div, README.md:31-54) plus the session and test entry points.
 #include <chrono>
+#include <memory>
+#include <thread>
 #include <cmath>
 #include <cstring>
 #include <functional>
@@ -143,6 +145,60 @@ void write_matrix(matrix A, const char* file) {
     });
 }
 
+namespace {
+
+// contiguous column blocks, dealt out in tile-wide (256-column) units as evenly as possible
+// (the rule of nmf_gpu_b200/sharding.py)
+void column_shard(long long N, int rank, int world, long long* first, long long* count) {
+    const long long mult = 256, nblocks = (N + mult - 1) / mult, base = nblocks / world, extra = nblocks % world;
+    const long long f = rank * base + std::min<long long>(rank, extra), c = base + (rank < extra ? 1 : 0);
+    *first = std::min(N, f * mult);
+    *count = std::min(N, (f + c) * mult) - *first;
+}
+
+// update_div on g GPUs of this box from ONE process: a host thread per GPU, X and H sharded by columns,
+// W replicated, one NCCL allreduce per iteration — what `NMF_NUM_GPUS=g ./nmf` runs.
+void update_div_multi(matrix W, matrix H, matrix X, float thresh, int max_iter, double t[10], int verbose,
+                      const nmf_options& o, int g, nmf_result* res) {
+    const int M = W.dim[0], K = W.dim[1];
+    const long long N = H.dim[1];
+    unsigned char uid[128];
+    nccl_unique_id(uid);
+    const int dev0 = o.device >= 0 ? o.device : 0;
+    std::vector<std::thread> threads;
+    std::vector<std::string> errors((size_t)g);
+    std::vector<nmf_result> results((size_t)g);
+    for (int r = 0; r < g; ++r) {
+        threads.emplace_back([&, r] {
+            try {
+                long long first = 0, count = 0;
+                column_shard(N, r, g, &first, &count);
+                NMF_CHECK(count > 0, "update_div: fewer 256-column blocks than GPUs (lower NMF_NUM_GPUS)");
+                nmf_options orank = o;
+                orank.device = dev0 + r;
+                std::unique_ptr<nmf_session_impl> s(session_create(M, (int)count, K, first, N, orank));
+                nccl_join(*s, r, g, uid);
+                session_upload(*s, W.mat, H.mat + (size_t)first * K, X.mat + (size_t)first * M);
+                session_run(*s, thresh, max_iter, r == 0 ? t : nullptr, r == 0 ? verbose : 0, &results[(size_t)r]);
+                session_download(*s, r == 0 ? W.mat : nullptr, H.mat + (size_t)first * K);
+            } catch (const std::exception& e) {
+                errors[(size_t)r] = e.what();
+                if (errors[(size_t)r].empty()) errors[(size_t)r] = "unknown error";
+            }
+        });
+    }
+    for (auto& th : threads) th.join();
+    for (int r = 0; r < g; ++r) NMF_CHECK(errors[(size_t)r].empty(), "GPU " + std::to_string(dev0 + r) + ": " + errors[(size_t)r]);
+    if (res) *res = results[0];
+}
+
+int env_num_gpus() {
+    const char* v = std::getenv("NMF_NUM_GPUS");
+    return (v && *v) ? std::max(1, std::atoi(v)) : 1;
+}
+
+}  // namespace
+
 int nmf_update_div_ex(matrix W, matrix H, matrix X, float CONVERGE_THRESH, int max_iter, double t[10],
                       int verbose, const nmf_options* opt, nmf_result* res) {
     return guarded([&] {
@@ -151,6 +207,16 @@ int nmf_update_div_ex(matrix W, matrix H, matrix X, float CONVERGE_THRESH, int m
         check_shapes(W, H, X);
         NMF_CHECK(max_iter >= 0, "update_div: max_iter must be >= 0");
         const nmf_options o = resolve(opt);
+        // the GPU count is not in the reference's signature (README.md:39-47): NMF_NUM_GPUS selects it
+        int g = env_num_gpus();
+        if (g > 1) {
+            int ndev = 0;
+            CUDA_CHECK(cudaGetDeviceCount(&ndev));
+            NMF_CHECK((o.device >= 0 ? o.device : 0) + g <= ndev, "NMF_NUM_GPUS exceeds the visible devices");
+            update_div_multi(W, H, X, CONVERGE_THRESH, max_iter, t, verbose, o, g, res);
+            if (t) t[PH_TOTAL] = std::chrono::duration<double>(clk::now() - w0).count();
+            return;
+        }
         nmf_session_impl* s = session_create(W.dim[0], H.dim[1], W.dim[1], 0, H.dim[1], o);
         try {
             session_upload(*s, W.mat, H.mat, X.mat);
