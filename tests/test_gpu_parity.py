@@ -91,7 +91,8 @@ def test_sums(api, engine, mode):
 
 @pytest.mark.parametrize("engine", ENGINES)
 @pytest.mark.parametrize("mode", ["exact", "refcompat"])
-@pytest.mark.parametrize("shape", [(256, 512, 64), (130, 70, 40), (1100, 90, 33), (300, 700, 160), (600, 1300, 256)])
+@pytest.mark.parametrize("shape", [(256, 512, 64), (130, 70, 40), (1100, 90, 33), (300, 700, 160), (600, 1300, 256),
+                                   (200, 600, 320)])
 def test_half_steps(api, oracle, engine, mode, shape):
     M, N, K = shape
     W, H, X = rand_problem(M, N, K, seed=K)
@@ -175,6 +176,18 @@ def test_c2_shape_small_k(api, oracle, engine):
     Wo, Ho, _, cost = oracle.update_div(W, H, X, 0.0, 30, "exact", acc64=True)
     assert max_rel(Wd, Wo) <= 1e-4 and max_rel(Hd, Ho) <= 1e-4
     assert abs(oracle.kl(Wd, Hd, X) - cost) / cost <= 1e-5
+
+
+@pytest.mark.parametrize("shape", [(1, 1, 1), (5, 3, 2), (33, 1, 7), (1, 300, 3), (257, 129, 1)])
+def test_degenerate_shapes(api, oracle, shape):
+    """extents of 1 and far below a tile: TMA out-of-bounds fill and the row/column predicates carry them"""
+    M, N, K = shape
+    W, H, X = rand_problem(M, N, K, seed=M * 7 + N)
+    Wd = W.copy(order="F"); Hd = H.copy(order="F")
+    res = api.update_div(Wd, Hd, X, 0.0, 10)
+    Wo, Ho, _, cost = oracle.update_div(W, H, X, 0.0, 10, "exact", acc64=True)
+    assert res.iterations == 10
+    assert max_rel(Wd, Wo) <= 1e-4 and max_rel(Hd, Ho) <= 1e-4
 
 
 @pytest.mark.parametrize("engine", ENGINES)
