@@ -17,7 +17,7 @@ for name, (W, H, X) in cases.items():
     Wo, Ho, _, co = oracle.update_div(W, H, X, 0.0, 100, "exact", acc64=True)
     Wf, Hf, _, cf = oracle.update_div(W, H, X, 0.0, 100, "exact", acc64=False)
     print(f"{name}: oracle fp32 vs fp64: W {max_rel(Wf, Wo):.2e} H {max_rel(Hf, Ho):.2e}")
-    for chunk in ("1", "4"):
+    for chunk in (os.environ.get("MARGIN_CHUNKS", "1,4").split(",")):
         os.environ["NMF_UMMA_CHUNK"] = chunk
         Wd = W.copy(order="F"); Hd = H.copy(order="F")
         api.update_div(Wd, Hd, X, 0.0, 100)
