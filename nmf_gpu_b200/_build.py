@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libnmf_b200.so")
 SOURCES = ["api.cpp", "dist.cpp", "session.cu", "kernels_small.cu", "kernels_simt.cu", "kernels_umma.cu"]
-HEADERS = ["common.hpp", "session.hpp", "umma_ptx.cuh", "umma_host.inc", os.path.join("..", "..", "include", "nmf.h")]
+HEADERS = ["common.hpp", "session.hpp", "umma_ptx.cuh", "tf32.cuh", "umma_host.inc", "umma_fused.inc", os.path.join("..", "..", "include", "nmf.h")]
 
 
 def nvcc_path():

@@ -331,8 +331,8 @@ int nmf_dbg_w_step(float* W, const float* H, const float* X, int M, int N, int K
                 simt_quotient(s.W, s.H, s.X, s.Y, nullptr, s.d, s.stream);
                 simt_numer(s.Y, s.H, s.packed, s.d, s.stream);
             } else {
-                umma::quotient(s, false);
-                umma::numer(s);
+                if (umma::fused_w_enabled(s)) umma::fused_w(s);
+                else { umma::quotient(s, false); umma::numer(s); }
                 if (s.nsplit > 1) { P = s.Psplit; nsplit = s.nsplit; stride = s.d.szW(); }
             }
             launch_update_w(s.W, s.Whi, s.Wlo, P, nsplit, stride, s.sumH, s.d, s.stream);

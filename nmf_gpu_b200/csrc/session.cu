@@ -239,15 +239,21 @@ void iteration_rest(nmf_session_impl& s, PhaseTimer* pt) {
     });
     // sum rows of H (nmf.cu:164) into the packed buffer's tail
     PHASE(pt, PH_SUMS, { launch_rowsum(s.H, s.rowsum_partials, s.sumH, d, s.stream); count_launches(s, 2); });
-    // Z = X ./ max(W*H, EPS) with the new H (nmf.cu:155-161)
-    PHASE(pt, PH_QUOT, do_quotient(s, false));
-    // numerator Z*H' (nmf.cu:168): split over column blocks, partials reduced in order by the W update
     const float* P = s.packed; int nsplit = 1; size_t stride = 0;
-    PHASE(pt, PH_GEMM2, {
-        if (s.opt.engine == NMF_ENGINE_SIMT) simt_numer(s.Y, s.H, s.packed, d, s.stream);
-        else umma::numer(s);
-        count_launches(s, 1);
-    });
+    if (s.opt.engine == NMF_ENGINE_TCGEN05 && umma::fused_w_enabled(s)) {
+        // both of the steps below in one kernel: the quotient goes from TMEM through shared memory into the
+        // second MMA and never reaches HBM
+        PHASE(pt, PH_GEMM2, { umma::fused_w(s); count_launches(s, 1); });
+    } else {
+        // Z = X ./ max(W*H, EPS) with the new H (nmf.cu:155-161)
+        PHASE(pt, PH_QUOT, do_quotient(s, false));
+        // numerator Z*H' (nmf.cu:168): split over column blocks, partials reduced in order by the W update
+        PHASE(pt, PH_GEMM2, {
+            if (s.opt.engine == NMF_ENGINE_SIMT) simt_numer(s.Y, s.H, s.packed, d, s.stream);
+            else umma::numer(s);
+            count_launches(s, 1);
+        });
+    }
     if (s.opt.engine == NMF_ENGINE_TCGEN05 && s.nsplit > 1) { P = s.Psplit; nsplit = s.nsplit; stride = d.szW(); }
     if (s.nranks > 1) {
         // One exchange per iteration: [numerator | row sums of H] summed over the column shards.

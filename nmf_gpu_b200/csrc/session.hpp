@@ -68,6 +68,9 @@ int   updh_splits(const Dims& d);
 void  quotient(nmf_session_impl& s, bool with_cost);
 void  update_h(nmf_session_impl& s);
 void  numer(nmf_session_impl& s);
+// fused W step: second quotient + numerator in one kernel, the quotient never reaches HBM (umma_fused.inc)
+bool  fused_w_enabled(const nmf_session_impl& s);
+void  fused_w(nmf_session_impl& s);
 // raw contraction for descriptor bring-up (nmf_dbg_gemm)
 void  dbg_gemm(int which, const float* dA, const float* dB, float* dC, int M, int N, int K, int passes,
                cudaStream_t st);

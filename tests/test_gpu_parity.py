@@ -121,6 +121,22 @@ def test_h_step_tile_modes(api, oracle, hsplit, pair, monkeypatch):
     assert max_rel(W1, oracle.w_step(W, H, X, "exact", acc64=True)) < 2e-5
 
 
+@pytest.mark.parametrize("shape", [(300, 700, 64), (600, 1300, 256), (520, 3000, 128), (257, 8200, 192), (1024, 290, 256)])
+def test_fused_w_step(api, oracle, shape, monkeypatch):
+    """the fused W step (umma_fused.inc: quotient tile -> TF32 pair in shared memory -> second MMA, the
+    quotient never in HBM) against the oracle and against the two-kernel path; ragged row blocks, a last
+    column tile with fewer than 8 chunks, P tiles of 64..256 columns"""
+    M, N, K = shape
+    W, H, X = rand_problem(M, N, K, seed=K + 1)
+    ref = oracle.w_step(W, H, X, "exact", acc64=True)
+    monkeypatch.setenv("NMF_UMMA_FUSE", "0")
+    W0 = api.dbg_w_step(W, H, X, api.options())
+    monkeypatch.setenv("NMF_UMMA_FUSE", "2")
+    W1 = api.dbg_w_step(W, H, X, api.options())
+    assert max_rel(W1, ref) < 2e-5
+    assert max_rel(W1, W0) < 1e-5
+
+
 @pytest.mark.parametrize("chunk", [1, 4, 16])
 def test_chunk_period_bounds_truncation_bias(api, chunk, monkeypatch):
     """tcgen05.mma truncates its fp32 accumulator, so an all-positive reduction comes out low by an
