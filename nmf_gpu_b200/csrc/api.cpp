@@ -313,9 +313,14 @@ int nmf_dbg_quotient(const float* W, const float* H, const float* X, float* Y, d
 int nmf_dbg_h_step(const float* W, float* H, const float* X, int M, int N, int K, const nmf_options* opt) {
     return guarded([&] {
         with_session(W, H, X, M, N, K, opt, [&](nmf_session_impl& s) {
-            iteration_head(s, false, nullptr);
-            if (s.opt.engine == NMF_ENGINE_SIMT) simt_update_h(s.W, s.Y, s.sumW, s.H, s.d, s.stream);
-            else umma::update_h(s);
+            if (s.opt.engine == NMF_ENGINE_TCGEN05 && umma::fused_h_enabled(s)) {
+                launch_colsum(s.W, s.sumW, s.d, s.stream);
+                umma::fused_h(s);
+            } else {
+                iteration_head(s, false, nullptr);
+                if (s.opt.engine == NMF_ENGINE_SIMT) simt_update_h(s.W, s.Y, s.sumW, s.H, s.d, s.stream);
+                else umma::update_h(s);
+            }
             session_download(s, nullptr, H);
         });
     });

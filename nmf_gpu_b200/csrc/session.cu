@@ -229,6 +229,8 @@ void iteration_head(nmf_session_impl& s, bool with_cost, PhaseTimer* pt) {
     PHASE(pt, PH_QUOT, do_quotient(s, with_cost));
 }
 
+static void w_half(nmf_session_impl& s, PhaseTimer* pt);
+
 void iteration_rest(nmf_session_impl& s, PhaseTimer* pt) {
     const Dims& d = s.d;
     // H = H .* ((W'*Z) ./ sumW)   (nmf.cu:138-145)
@@ -237,6 +239,23 @@ void iteration_rest(nmf_session_impl& s, PhaseTimer* pt) {
         else umma::update_h(s);
         count_launches(s, (s.opt.engine == NMF_ENGINE_TCGEN05 && s.hsplit > 1) ? 2 : 1);   // split: GEMM partials + fold/update kernel
     });
+    w_half(s, pt);
+}
+
+// One whole iteration when no cost is wanted: with the fused H step the first quotient never reaches HBM.
+void iteration_full(nmf_session_impl& s, PhaseTimer* pt) {
+    if (s.opt.engine == NMF_ENGINE_TCGEN05 && umma::fused_h_enabled(s)) {
+        PHASE(pt, PH_SUMS, { launch_colsum(s.W, s.sumW, s.d, s.stream); count_launches(s, 1); });
+        PHASE(pt, PH_GEMM2, { umma::fused_h(s); count_launches(s, 1); });
+        w_half(s, pt);
+    } else {
+        iteration_head(s, false, pt);
+        iteration_rest(s, pt);
+    }
+}
+
+static void w_half(nmf_session_impl& s, PhaseTimer* pt) {
+    const Dims& d = s.d;
     // sum rows of H (nmf.cu:164) into the packed buffer's tail
     PHASE(pt, PH_SUMS, { launch_rowsum(s.H, s.rowsum_partials, s.sumH, d, s.stream); count_launches(s, 2); });
     const float* P = s.packed; int nsplit = 1; size_t stride = 0;
@@ -285,9 +304,8 @@ static void build_graphs(nmf_session_impl& s) {
     cudaGraph_t g = nullptr;
     long long c0 = s.launches;
     CUDA_CHECK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));   // as nmf.cu:103
-    iteration_head(s, false, nullptr);
+    iteration_full(s, nullptr);
     const long long c1 = s.launches;
-    iteration_rest(s, nullptr);
     CUDA_CHECK(cudaStreamEndCapture(s.stream, &g));
     CUDA_CHECK(cudaGraphInstantiate(&s.g_full, g, 0));
     CUDA_CHECK(cudaGraphDestroy(g));
@@ -344,8 +362,7 @@ void session_run(nmf_session_impl& s, float thresh, int max_iter, double t[10], 
         } else if (graph) {
             CUDA_CHECK(cudaGraphLaunch(s.g_full, s.stream)); s.launches += s.launches_full;
         } else {
-            iteration_head(s, false, pt);
-            iteration_rest(s, pt);
+            iteration_full(s, pt);
         }
         done = it;
     }

@@ -49,6 +49,7 @@ struct PhaseTimer;   // session.cu
 // iteration pieces (session.cu)
 void iteration_head(nmf_session_impl& s, bool with_cost, PhaseTimer* pt);   // colsum(W); Y = quotient (+cost partials)
 void iteration_rest(nmf_session_impl& s, PhaseTimer* pt);                   // H update; rowsum; quotient; numerator; [allreduce]; W update
+void iteration_full(nmf_session_impl& s, PhaseTimer* pt);                   // one whole iteration without a cost (fused H step when enabled)
 
 // NCCL (dist.cpp)
 int  nccl_unique_id(void* id128);
@@ -71,6 +72,9 @@ void  numer(nmf_session_impl& s);
 // fused W step: second quotient + numerator in one kernel, the quotient never reaches HBM (umma_fused.inc)
 bool  fused_w_enabled(const nmf_session_impl& s);
 void  fused_w(nmf_session_impl& s);
+// fused H step: first quotient + W'*Y + the H update in one kernel (needs sumW)
+bool  fused_h_enabled(const nmf_session_impl& s);
+void  fused_h(nmf_session_impl& s);
 // raw contraction for descriptor bring-up (nmf_dbg_gemm)
 void  dbg_gemm(int which, const float* dA, const float* dB, float* dC, int M, int N, int K, int passes,
                cudaStream_t st);

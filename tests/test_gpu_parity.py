@@ -121,7 +121,10 @@ def test_h_step_tile_modes(api, oracle, hsplit, pair, monkeypatch):
     assert max_rel(W1, oracle.w_step(W, H, X, "exact", acc64=True)) < 2e-5
 
 
-@pytest.mark.parametrize("shape", [(300, 700, 64), (600, 1300, 256), (520, 3000, 128), (257, 8200, 192), (1024, 290, 256)])
+FUSED_SHAPES = [(300, 700, 64), (600, 1300, 256), (520, 3000, 128), (257, 8200, 192), (1024, 290, 256)]
+
+
+@pytest.mark.parametrize("shape", FUSED_SHAPES)
 def test_fused_w_step(api, oracle, shape, monkeypatch):
     """the fused W step (umma_fused.inc: quotient tile -> TF32 pair in shared memory -> second MMA, the
     quotient never in HBM) against the oracle and against the two-kernel path; ragged row blocks, a last
@@ -135,6 +138,36 @@ def test_fused_w_step(api, oracle, shape, monkeypatch):
     W1 = api.dbg_w_step(W, H, X, api.options())
     assert max_rel(W1, ref) < 2e-5
     assert max_rel(W1, W0) < 1e-5
+
+
+@pytest.mark.parametrize("mode", ["exact", "refcompat"])
+@pytest.mark.parametrize("shape", FUSED_SHAPES)
+def test_fused_h_step(api, oracle, shape, mode, monkeypatch):
+    """the fused H step (the transposed arrangement: S' = H'W' with the columns of H on the TMEM lanes, the H
+    update as the kernel's epilogue) against the oracle and the two-kernel path"""
+    M, N, K = shape
+    W, H, X = rand_problem(M, N, K, seed=K + 2)
+    ref = oracle.h_step(W, H, X, mode, acc64=True)
+    monkeypatch.setenv("NMF_UMMA_FUSE", "0")
+    H0 = api.dbg_h_step(W, H, X, api.options(semantics=mode))
+    monkeypatch.setenv("NMF_UMMA_FUSE", "2")
+    H1 = api.dbg_h_step(W, H, X, api.options(semantics=mode))
+    assert max_rel(H1, ref) < 2e-5
+    assert max_rel(H1, H0) < 1e-5
+
+
+@pytest.mark.parametrize("graph", [True, False])
+def test_fused_iterations_c1(api, oracle, c1, graph, monkeypatch):
+    """100 iterations of C1 with both half-iterations fused, cost checks every 25 (those iterations take the
+    two-kernel H step, whose quotient carries the cost): the north-star tolerance against the fp64 oracle"""
+    monkeypatch.setenv("NMF_UMMA_FUSE", "2")
+    W, H, X = c1["W"], c1["H"], c1["X"]
+    Wo, Ho, _, cost = oracle.update_div(W, H, X, 0.0, 100, "exact", acc64=True)
+    Wd, Hd = W.copy(order="F"), H.copy(order="F")
+    res = api.update_div(Wd, Hd, X, 1e-12, 100, opt=api.options(use_graph=graph))
+    assert res.iterations == 100
+    assert max_rel(Wd, Wo) < 1e-4 and max_rel(Hd, Ho) < 1e-4
+    assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
 
 
 @pytest.mark.parametrize("chunk", [1, 4, 16])
