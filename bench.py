@@ -198,23 +198,46 @@ def main():
     barrier()
     sess.run(0.0, 3, t=t)
     barrier()
-    quot_ms = t[0] * 1e3 / (2 * 3)                            # 2 quotient launches per iteration
-    gemm2_ms = t[3] * 1e3 / (2 * 3)                           # update_h + numerator
+    fused = sess.fused_steps()                                # bit 0: W step, bit 1: H step run as one kernel each
+    nq = 2 - bin(fused).count("1")                            # stand-alone quotient launches per iteration
+    quot_ms = t[0] * 1e3 / (nq * 3) if nq else 0.0
+    gemm2_ms = t[3] * 1e3 / (2 * 3)                           # the H-step and W-step GEMM kernels (fused: incl. their quotient)
     pk = peaks()
     peak3 = pk["bf16_sustained"] / 2.0 / 3.0                  # TF32 dense = bf16/2; 3 MMAs per product
-    # dominant kernel = k_umma<QUOT> (W*H with the fused clamp/divide), 2*M*n_loc*K algorithmic flop per launch
-    ach = 2.0 * M * n_loc * K / (quot_ms * 1e-3) / 1e12 if quot_ms > 0 else 0.0
     traffic = None
     try:   # DRAM bytes per launch of the same kernel from the committed ncu --set full capture (profiles/)
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get(str(world))
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic = tj.get(args.workload + ("+fused" if fused == 3 else ""), {}).get(str(world))
     except (OSError, ValueError):
         pass
-    roofline = {"bound": "tensor", "kernel": "k_umma<QUOT> (W*H GEMM + fused X./max(.,EPS), 3xTF32)",
+    if fused == 3:
+        # dominant kernel = k_fused (quotient GEMM + consuming GEMM in one launch): 4*M*n_loc*K algorithmic flop per launch
+        ach = 4.0 * M * n_loc * K / (gemm2_ms * 1e-3) / 1e12 if gemm2_ms > 0 else 0.0
+        kernel = "k_fused<W step | H step> (W*H GEMM -> X./max(.,EPS) -> TF32 pair in smem -> second GEMM, 3xTF32)"
+        launch_ms = gemm2_ms
+        alg_bytes = 4.0 * M * n_loc + 8.0 * K * (M + n_loc) + 12.0 * K * min(M, n_loc)   # X read once; W, H pairs; the small output
+    else:
+        # dominant kernel = k_umma<QUOT> (W*H with the fused clamp/divide), 2*M*n_loc*K algorithmic flop per launch
+        ach = 2.0 * M * n_loc * K / (quot_ms * 1e-3) / 1e12 if quot_ms > 0 else 0.0
+        kernel = "k_umma<QUOT> (W*H GEMM + fused X./max(.,EPS), 3xTF32)"
+        launch_ms = quot_ms
+        alg_bytes = 8.0 * M * n_loc + 8.0 * K * (M + n_loc)   # X read + Y written once, W and H (hi, lo) read
+    # The denominator is MEASURED_PEAKS' cuBLAS bf16 figure / 2 (TF32) / 3 (three MMAs per product): the sustained one
+    # for a kernel inside a long step.  The fused kernels draw less power per flop than that cuBLAS run (no M x N
+    # round trip through HBM), so they clock higher and pass it; the burst figure is the ceiling then.  Both are
+    # power-capped clocks, so `frac_at_clock` also gives achieved / (148 SMs x 4096 TF32 flop/clk x the SM clock sampled
+    # during the timed region / 3), i.e. the tensor-pipe utilisation ncu reports.
+    peak_kind = "sustained"
+    if ach > peak3:
+        peak3, peak_kind = pk["bf16"] / 2.0 / 3.0, "burst"
+    clk_mhz = (clocks or {}).get("sm_mhz") if rank == 0 else None
+    frac_at_clock = ach / (148 * 4096 * clk_mhz * 1e6 / 3.0 / 1e12) if clk_mhz else None
+    roofline = {"bound": "tensor", "kernel": kernel,
                 "achieved": ach, "peak": peak3, "unit": "TFLOP/s", "frac": ach / peak3, "traffic": traffic,
-                "algorithmic_hbm_bytes": 8.0 * M * n_loc + 8.0 * K * (M + n_loc),   # X read + Y written once, W and H (hi, lo) read
-                "peak_note": f"{pk['source']}: bf16 sustained {pk['bf16_sustained']:.0f} TF/s / 2 (TF32) / 3 (3xTF32 passes)",
-                "launch_ms": quot_ms, "other_gemm_launch_ms": gemm2_ms,
-                "whole_iteration_frac": (flop_iter / world / (ms_per_step * 1e-3) / 1e12) / peak3,
+                "algorithmic_hbm_bytes": alg_bytes, "frac_at_clock": frac_at_clock,
+                "peak_note": f"{pk['source']}: bf16 {peak_kind} {pk['bf16'] if peak_kind == 'burst' else pk['bf16_sustained']:.0f} TF/s / 2 (TF32) / 3 (3xTF32 passes)",
+                "launch_ms": launch_ms, "other_gemm_launch_ms": gemm2_ms if fused != 3 else None, "fused_steps": fused,
+                "whole_iteration_frac": (flop_iter / world / (ms_per_step * 1e-3) / 1e12) / peak3,   # same denominator
                 "phase_seconds_3_iterations": [float(v) for v in t]}
     if world == 1:
         sess.close()      # N > 1: kept until the e2e run has shared its communicator (a process creates NCCL once)

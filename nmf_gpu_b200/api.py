@@ -79,6 +79,7 @@ _SIGNATURES = {
     "nmf_session_join": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
     "nmf_session_share_comm": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
     "nmf_session_fill_planted": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_ulonglong, ctypes.c_int, ctypes.c_float]),
+    "nmf_session_fused_steps": (ctypes.c_int, [ctypes.c_void_p]),
     "nmf_session_run": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_float, ctypes.c_int, _f64p, ctypes.c_int,
                                        ctypes.POINTER(nmf_result)]),
     "nmf_session_cost": (ctypes.c_int, [ctypes.c_void_p, _f64p]),
@@ -214,6 +215,10 @@ class Session:
 
     def fill_uniform(self, seed, which=7):
         _check(lib().nmf_session_fill_uniform(self._h, int(seed), int(which)))
+
+    def fused_steps(self):
+        """bit 0: W step fused, bit 1: H step fused (one kernel per half-iteration, the quotient never in HBM)"""
+        return int(lib().nmf_session_fused_steps(self._h))
 
     def fill_planted(self, seed, rank, noise=0.05):
         """X <- planted rank-`rank` product with +-noise multiplicative uniform noise (W, H untouched)"""

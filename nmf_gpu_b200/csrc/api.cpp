@@ -266,6 +266,11 @@ int nmf_session_share_comm(nmf_session* dst, nmf_session* src) {
     return guarded([&] { NMF_CHECK(dst && src, "NULL session"); nccl_share(*dst, *src); });
 }
 
+int nmf_session_fused_steps(const nmf_session* s) {
+    if (!s || s->opt.engine != NMF_ENGINE_TCGEN05) return 0;
+    return (umma::fused_w_enabled(*s) ? 1 : 0) | (umma::fused_h_enabled(*s) ? 2 : 0);
+}
+
 int nmf_nccl_unique_id(void* id128) { return guarded([&] { nccl_unique_id(id128); }); }
 int nmf_session_join(nmf_session* s, int rank, int nranks, const void* id128) {
     return guarded([&] { NMF_CHECK(s, "NULL session"); nccl_join(*s, rank, nranks, id128); });

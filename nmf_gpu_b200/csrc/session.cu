@@ -103,7 +103,8 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
             s->nsplit = umma::numer_splits(d);
             if (s->nsplit > 1) s->Psplit = dalloc<float>((size_t)s->nsplit * d.szW());
             s->hsplit = umma::updh_splits(d);
-            if (s->hsplit > 1) s->Hpart = dalloc<float>((size_t)s->hsplit * d.szHa());
+            s->fhsplit = umma::fused_h_splits(d, opt.tf32_passes);
+            if (std::max(s->hsplit, s->fhsplit) > 1) s->Hpart = dalloc<float>((size_t)std::max(s->hsplit, s->fhsplit) * d.szHa());
             s->plan = umma::plan_create(*s);
         }
         s->cost_partials = dalloc<double>(s->n_cost_partials > 0 ? s->n_cost_partials : 1);
@@ -246,7 +247,7 @@ void iteration_rest(nmf_session_impl& s, PhaseTimer* pt) {
 void iteration_full(nmf_session_impl& s, PhaseTimer* pt) {
     if (s.opt.engine == NMF_ENGINE_TCGEN05 && umma::fused_h_enabled(s)) {
         PHASE(pt, PH_SUMS, { launch_colsum(s.W, s.sumW, s.d, s.stream); count_launches(s, 1); });
-        PHASE(pt, PH_GEMM2, { umma::fused_h(s); count_launches(s, 1); });
+        PHASE(pt, PH_GEMM2, { const int n = umma::fused_h(s); count_launches(s, n); });
         w_half(s, pt);
     } else {
         iteration_head(s, false, pt);

@@ -24,6 +24,7 @@ struct nmf_session_impl {
     float *sumW = nullptr, *packed = nullptr, *sumH = nullptr /* = packed + Mv*Kv */;
     float *Psplit = nullptr; int nsplit = 1;      // split-N partial numerators (tcgen05 engine)
     float *Hpart = nullptr; int hsplit = 1;       // split-M partial W'*Y of the H update (small problems only)
+    int fhsplit = 1;                              // the same for the fused H step (shares Hpart)
     float *rowsum_partials = nullptr;
     double *cost_partials = nullptr; int n_cost_partials = 0;
     double *cost_dev = nullptr, *cost_host = nullptr /* pinned */;
@@ -74,7 +75,8 @@ bool  fused_w_enabled(const nmf_session_impl& s);
 void  fused_w(nmf_session_impl& s);
 // fused H step: first quotient + W'*Y + the H update in one kernel (needs sumW)
 bool  fused_h_enabled(const nmf_session_impl& s);
-void  fused_h(nmf_session_impl& s);
+int   fused_h(nmf_session_impl& s);                 // returns the kernels launched (2 when the rows of W are split)
+int   fused_h_splits(const Dims& d, int passes);
 // raw contraction for descriptor bring-up (nmf_dbg_gemm)
 void  dbg_gemm(int which, const float* dA, const float* dB, float* dC, int M, int N, int K, int passes,
                cudaStream_t st);

@@ -121,7 +121,8 @@ def test_h_step_tile_modes(api, oracle, hsplit, pair, monkeypatch):
     assert max_rel(W1, oracle.w_step(W, H, X, "exact", acc64=True)) < 2e-5
 
 
-FUSED_SHAPES = [(300, 700, 64), (600, 1300, 256), (520, 3000, 128), (257, 8200, 192), (1024, 290, 256)]
+FUSED_SHAPES = [(300, 700, 64), (600, 1300, 256), (520, 3000, 128), (257, 8200, 192), (1024, 290, 256),
+                (2100, 600, 128)]          # the last one splits the rows of W over work items in the H step
 
 
 @pytest.mark.parametrize("shape", FUSED_SHAPES)
