@@ -1,4 +1,7 @@
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -8 gpurun_out/pytest_gpu.log | cut -c1-300
+# round evidence on one B200: GPU test suite, small-workload lines, the C4 bench line, the ncu launch list of the
+# same command and one full capture of the two fused half-iteration kernels (each ncu pass only after the plain
+# command has exited 0)
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log | cut -c1-300
 for w in c1 c2; do
 timeout 600 python bench.py --workload $w --steps 50 --warmup 3 --no-cpu --no-e2e > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err; python - <<PY
 import json
@@ -8,4 +11,4 @@ PY
 done
 timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/bench_c4_n1.json 2> gpurun_out/bench_c4_n1.err; echo "bench rc=$?"; cat gpurun_out/bench_c4_n1.json | cut -c1-2500
 timeout 600 python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu > gpurun_out/plain.log 2>&1 && timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r1_launches_c4.csv python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu > gpurun_out/ncu_launch.log 2>&1; echo "ncu launches rc=$?"
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k_umma -s 8 -c 4 -o gpurun_out/r1_umma_c4 -f python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu > gpurun_out/ncu_full_c4.log 2>&1; echo "ncu full c4 rc=$?"
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k_fused -s 6 -c 2 -o gpurun_out/r1_fused_c4 -f python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu > gpurun_out/ncu_full_c4.log 2>&1; echo "ncu full c4 rc=$?"

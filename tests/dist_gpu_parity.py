@@ -22,7 +22,9 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     rank, world = dist.get_rank(), dist.get_world_size()
-    M, N, K, iters = 1024, max(4096, 1024 * world) + 300, 96, 30      # every rank owns columns (shards are 128-column blocks)
+    # every rank owns columns (shards are 256-column blocks); K a multiple of 64 so that NMF_UMMA_FUSE=2 runs the
+    # fused half-iteration kernels on every rank (the default only fuses large problems)
+    M, N, K, iters = 1024, max(4096, 1024 * world) + 300, 128, 30
     W, H, X = rand_problem(M, N, K, seed=11)
     out = {}
     for mode in ("exact", "refcompat"):
@@ -35,6 +37,7 @@ def main():
         dist.broadcast(uid, 0)
         s.join(rank, world, uid.cpu().numpy().tobytes())
         s.upload(W, H[:, lo:lo + n], X[:, lo:lo + n])
+        fused = s.fused_steps()
         res = s.run(1e-9, iters)                      # thresh > 0 exercises the allreduced cost too
         Wd, Hd = s.download()
         cost = s.cost()
@@ -57,7 +60,7 @@ def main():
                 W1, H1 = s1.download()
                 cost1 = s1.cost()
             out[mode] = dict(W=max_rel(Wd, W1), H=max_rel(Hm, H1), cost_rel=abs(cost - cost1) / abs(cost1),
-                             iters=(res.iterations, r1.iterations))
+                             iters=(res.iterations, r1.iterations), fused_steps=fused)
     ok = True
     if rank == 0:
         print("PARITY " + json.dumps(dict(world=world, **out)), flush=True)
