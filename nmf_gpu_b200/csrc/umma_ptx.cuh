@@ -243,6 +243,51 @@ __device__ __forceinline__ void mma_tf32_cg2_w(uint32_t d_tmem, uint32_t alo, ui
         :: "r"(d_tmem), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "r"(accumulate) : "memory");
 }
 
+
+// ---- the same mbarrier operations on 32-bit shared-space addresses -------------------------------
+// (a barrier passed as a generic pointer is converted with cvta at every use, and the compiler re-derives the
+// dynamic shared memory base from special registers (S2UR SR_CgaCtaId / SR_SWINHI, ~20 cycles each) in front of
+// every wait; the fused kernels compute one opaque 32-bit base and add constants)
+__device__ __forceinline__ bool mbar_try_wait_a(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred P;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, P;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity, unsigned int* err_flag, unsigned int code) {
+    uint32_t tries = 0;
+    while (!mbar_try_wait_a(bar, parity)) {
+        if (++tries > (1u << 24)) {
+            if (err_flag) atomicExch(err_flag, code);
+            __threadfence_system();
+            __trap();
+        }
+    }
+}
+__device__ __forceinline__ void mbar_arrive_a(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx_a(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_hint_a(uint32_t smem_dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, uint64_t pol) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
+        :: "r"(smem_dst), "l"((uint64_t)m), "r"(bar), "r"(c0), "r"(c1), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_cg2_a(uint32_t smem_dst, const CUtensorMap* m, uint32_t bar_cluster, int c0, int c1, uint64_t pol) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
+        :: "r"(smem_dst), "l"((uint64_t)m), "r"(bar_cluster), "r"(c0), "r"(c1), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void mma_commit_cg2_a(uint32_t bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 :: "r"(bar), "h"(mask) : "memory");
+}
+
 // ---- descriptors ---------------------------------------------------------------------------
 // Shared-memory matrix descriptor (sm_100 "version 1"), 128-byte swizzle:
 //   [0,14) start >> 4 | [16,30) leading byte offset >> 4 | [32,46) stride byte offset >> 4 |
