@@ -157,6 +157,19 @@ def test_fused_h_step(api, oracle, shape, mode, monkeypatch):
     assert max_rel(H1, H0) < 1e-5
 
 
+@pytest.mark.parametrize("nw", ["2", "4"])
+def test_fused_worker_warp_variants(api, oracle, nw, monkeypatch):
+    """K <= 128 runs 4 worker warps per TMEM lane quadrant by default (the quotient bounds the kernel there), K > 128
+    two; NMF_UMMA_FUSE_NW forces either on a K = 128 problem"""
+    monkeypatch.setenv("NMF_UMMA_FUSE", "2")
+    monkeypatch.setenv("NMF_UMMA_FUSE_NW", nw)
+    W, H, X = rand_problem(700, 1500, 128, seed=9)
+    H1 = api.dbg_h_step(W, H, X, api.options())
+    assert max_rel(H1, oracle.h_step(W, H, X, "exact", acc64=True)) < 2e-5
+    W1 = api.dbg_w_step(W, H, X, api.options())
+    assert max_rel(W1, oracle.w_step(W, H, X, "exact", acc64=True)) < 2e-5
+
+
 @pytest.mark.parametrize("graph", [True, False])
 def test_fused_iterations_c1(api, oracle, c1, graph, monkeypatch):
     """100 iterations of C1 with both half-iterations fused, cost checks every 25 (those iterations take the
