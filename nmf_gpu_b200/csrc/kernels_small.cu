@@ -224,13 +224,22 @@ __global__ void __launch_bounds__(256) k_fold_splits(const float* __restrict__ P
     }
 }
 
-__global__ void k_sum_partials(const double* __restrict__ partials, int n, double* __restrict__ out) {
-    // one warp; lane-strided ordered sums then a fixed shuffle tree: deterministic.
+__global__ void __launch_bounds__(1024) k_sum_partials(const double* __restrict__ partials, int n, double* __restrict__ out) {
+    // one block; thread-strided ordered sums, a fixed shuffle tree per warp, then warp 0 over the 32 warp sums:
+    // deterministic (no atomics), and wide enough for the ~1e5 per-warp partials of the fused H step
+    __shared__ double wsum[32];
     double s = 0.0;
-    for (int i = threadIdx.x; i < n; i += 32) s += partials[i];
+    for (int i = threadIdx.x; i < n; i += 1024) s += partials[i];
     #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (threadIdx.x == 0) *out = s;
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        s = wsum[threadIdx.x];
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (threadIdx.x == 0) *out = s;
+    }
 }
 
 inline int grid_for(size_t total, int block, int max_blocks = 148 * 16) {
@@ -310,7 +319,7 @@ void launch_fold_splits(const float* P, int nsplit, size_t split_stride, float* 
 }
 
 void launch_sum_partials(const double* partials, int n, double* out, cudaStream_t st) {
-    k_sum_partials<<<1, 32, 0, st>>>(partials, n, out);
+    k_sum_partials<<<1, 1024, 0, st>>>(partials, n, out);
     CUDA_CHECK_LAUNCH();
 }
 

@@ -59,7 +59,7 @@ nmf_session_impl::~nmf_session_impl() {
     if (g_rest) cudaGraphExecDestroy(g_rest);
     if (plan) umma::plan_destroy(plan);
     if (nccl) nccl_destroy(nccl);
-    float* fl[] = {W, H, X, Y, Whi, Wlo, Hhi, Hlo, sumW, packed, Psplit, Hpart, rowsum_partials};
+    float* fl[] = {W, H, X, Y, Whi, Wlo, Hhi, Hlo, sumW, packed, Psplit, Hpart, rowsum_partials, Hbak};
     for (float* p : fl) if (p) cudaFree(p);
     if (cost_partials) cudaFree(cost_partials);
     if (cost_dev) cudaFree(cost_dev);
@@ -100,6 +100,7 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
             s->Whi = dalloc<float>(d.szW()); s->Wlo = dalloc<float>(d.szW());
             s->Hhi = dalloc<float>(d.szHa()); s->Hlo = dalloc<float>(d.szHa());
             s->n_cost_partials = umma::cost_partial_count(d);
+            s->n_cost_partials_fused = umma::fused_cost_partial_count(d, opt.tf32_passes);
             s->nsplit = umma::numer_splits(d);
             if (s->nsplit > 1) s->Psplit = dalloc<float>((size_t)s->nsplit * d.szW());
             s->hsplit = umma::updh_splits(d);
@@ -107,7 +108,7 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
             if (std::max(s->hsplit, s->fhsplit) > 1) s->Hpart = dalloc<float>((size_t)std::max(s->hsplit, s->fhsplit) * d.szHa());
             s->plan = umma::plan_create(*s);
         }
-        s->cost_partials = dalloc<double>(s->n_cost_partials > 0 ? s->n_cost_partials : 1);
+        s->cost_partials = dalloc<double>(std::max(1, std::max(s->n_cost_partials, s->n_cost_partials_fused)));
         CUDA_CHECK(cudaStreamSynchronize(s->stream));
     } catch (...) {
         delete s;
@@ -232,6 +233,27 @@ void iteration_head(nmf_session_impl& s, bool with_cost, PhaseTimer* pt) {
 
 static void w_half(nmf_session_impl& s, PhaseTimer* pt);
 
+// Check iteration with the fused H step: the KL cost of the factors the iteration starts from is a by-product of
+// that step's quotient, which also rewrites H.  H is saved first so that a run that turns out to have converged
+// can hand back the factors the cost belongs to (the oracle stops before this H step).
+static bool fused_check_enabled(const nmf_session_impl& s) {
+    return s.opt.engine == NMF_ENGINE_TCGEN05 && umma::fused_h_enabled(s) && s.n_cost_partials_fused > 0;
+}
+static void iteration_head_fused_cost(nmf_session_impl& s, PhaseTimer* pt) {
+    const Dims& d = s.d;
+    if (!s.Hbak) s.Hbak = dalloc<float>(d.szHa());
+    PHASE(pt, PH_SUMS, { launch_colsum(s.W, s.sumW, d, s.stream); count_launches(s, 1); });
+    PHASE(pt, PH_COST, CUDA_CHECK(cudaMemcpyAsync(s.Hbak, s.H, d.szHa() * 4, cudaMemcpyDeviceToDevice, s.stream)));
+    PHASE(pt, PH_GEMM2, {
+        const int n = umma::fused_h(s, true); count_launches(s, n);
+        launch_sum_partials(s.cost_partials, s.n_cost_partials_fused, s.cost_dev, s.stream); count_launches(s, 1);
+    });
+}
+static void restore_h(nmf_session_impl& s) {
+    CUDA_CHECK(cudaMemcpyAsync(s.H, s.Hbak, s.d.szHa() * 4, cudaMemcpyDeviceToDevice, s.stream));
+    launch_split_tf32(s.H, s.Hhi, s.Hlo, s.d.szH(), s.stream); count_launches(s, 1);
+}
+
 void iteration_rest(nmf_session_impl& s, PhaseTimer* pt) {
     const Dims& d = s.d;
     // H = H .* ((W'*Z) ./ sumW)   (nmf.cu:138-145)
@@ -350,15 +372,17 @@ void session_run(nmf_session_impl& s, float thresh, int max_iter, double t[10], 
         // The cost after iteration it-1 is a by-product of iteration it's first quotient.
         const bool check = need_cost && it > 1 && ((it - 1) % every == 0);
         if (check) {
-            iteration_head(s, true, pt);
+            const bool fcheck = fused_check_enabled(s);
+            if (fcheck) iteration_head_fused_cost(s, pt); else iteration_head(s, true, pt);
             const auto c0 = clk::now();
             cost = read_cost(s);
             t_cost += std::chrono::duration<double>(clk::now() - c0).count();
             const double rel = (prev - cost) / cost;
             if (verbose) std::printf("iter %d  cost %.9g  rel.change %.3g\n", it - 1, cost, rel);
-            if (thresh > 0.0f && rel < (double)thresh) { converged = 1; break; }
+            if (thresh > 0.0f && rel < (double)thresh) { if (fcheck) restore_h(s); converged = 1; break; }
             prev = cost;
-            if (graph) { CUDA_CHECK(cudaGraphLaunch(s.g_rest, s.stream)); s.launches += s.launches_rest; }
+            if (fcheck) w_half(s, pt);
+            else if (graph) { CUDA_CHECK(cudaGraphLaunch(s.g_rest, s.stream)); s.launches += s.launches_rest; }
             else iteration_rest(s, pt);
         } else if (graph) {
             CUDA_CHECK(cudaGraphLaunch(s.g_full, s.stream)); s.launches += s.launches_full;

@@ -27,6 +27,8 @@ struct nmf_session_impl {
     int fhsplit = 1;                              // the same for the fused H step (shares Hpart)
     float *rowsum_partials = nullptr;
     double *cost_partials = nullptr; int n_cost_partials = 0;
+    int n_cost_partials_fused = 0;                // partials of the fused H step's cost variant (0: that step is not fused)
+    float *Hbak = nullptr;                        // H before a fused H step that carries the cost (allocated on first use)
     double *cost_dev = nullptr, *cost_host = nullptr /* pinned */;
 
     umma::Plan* plan = nullptr;
@@ -75,8 +77,9 @@ bool  fused_w_enabled(const nmf_session_impl& s);
 void  fused_w(nmf_session_impl& s);
 // fused H step: first quotient + W'*Y + the H update in one kernel (needs sumW)
 bool  fused_h_enabled(const nmf_session_impl& s);
-int   fused_h(nmf_session_impl& s);                 // returns the kernels launched (2 when the rows of W are split)
+int   fused_h(nmf_session_impl& s, bool with_cost = false);   // returns the kernels launched (2 when the rows of W are split)
 int   fused_h_splits(const Dims& d, int passes);
+int   fused_cost_partial_count(const Dims& d, int passes);
 // raw contraction for descriptor bring-up (nmf_dbg_gemm)
 void  dbg_gemm(int which, const float* dA, const float* dB, float* dC, int M, int N, int K, int passes,
                cudaStream_t st);

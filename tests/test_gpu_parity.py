@@ -93,7 +93,13 @@ def test_sums(api, engine, mode):
 @pytest.mark.parametrize("mode", ["exact", "refcompat"])
 @pytest.mark.parametrize("shape", [(256, 512, 64), (130, 70, 40), (1100, 90, 33), (300, 700, 160), (600, 1300, 256),
                                    (200, 600, 320)])
-def test_half_steps(api, oracle, engine, mode, shape):
+@pytest.mark.parametrize("fuse", ["0", "1"])
+def test_half_steps(api, oracle, engine, mode, shape, fuse, monkeypatch):
+    """fuse: the two-kernel path (quotient kernel + the GEMM that consumes it) / the default (one fused kernel per
+    half-iteration wherever K_v is a multiple of 64 and <= 256)"""
+    if engine != "tcgen05" and fuse == "1":
+        pytest.skip("fusion is a tcgen05-engine choice")
+    monkeypatch.setenv("NMF_UMMA_FUSE", fuse)
     M, N, K = shape
     W, H, X = rand_problem(M, N, K, seed=K)
     opt = api.options(semantics=mode, engine=engine)
@@ -110,6 +116,7 @@ def test_h_step_tile_modes(api, oracle, hsplit, pair, monkeypatch):
     fused epilogue (hsplit 1), a forced 3-way split of the reduction over the rows of W (partials
     folded by k_update_h) and the automatic choice; wide enough (38+ column tiles) that the automatic
     choice keeps the fused epilogue"""
+    monkeypatch.setenv("NMF_UMMA_FUSE", "0")
     monkeypatch.setenv("NMF_UMMA_PAIR", pair)
     if hsplit:
         monkeypatch.setenv("NMF_UMMA_HSPLIT", hsplit)
@@ -172,8 +179,8 @@ def test_fused_worker_warp_variants(api, oracle, nw, monkeypatch):
 
 @pytest.mark.parametrize("graph", [True, False])
 def test_fused_iterations_c1(api, oracle, c1, graph, monkeypatch):
-    """100 iterations of C1 with both half-iterations fused, cost checks every 25 (those iterations take the
-    two-kernel H step, whose quotient carries the cost): the north-star tolerance against the fp64 oracle"""
+    """100 iterations of C1 with both half-iterations fused, cost checks every 25 (the COST instantiation of the
+    fused H step): the north-star tolerance against the fp64 oracle"""
     monkeypatch.setenv("NMF_UMMA_FUSE", "2")
     W, H, X = c1["W"], c1["H"], c1["X"]
     Wo, Ho, _, cost = oracle.update_div(W, H, X, 0.0, 100, "exact", acc64=True)
@@ -182,6 +189,43 @@ def test_fused_iterations_c1(api, oracle, c1, graph, monkeypatch):
     assert res.iterations == 100
     assert max_rel(Wd, Wo) < 1e-4 and max_rel(Hd, Ho) < 1e-4
     assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
+
+
+@pytest.mark.parametrize("shape", [(300, 700, 64), (600, 1300, 256), (520, 3000, 128), (2100, 600, 64)])
+def test_fused_h_step_carries_the_cost(api, oracle, shape, monkeypatch):
+    """check iterations with the fused H step: the KL cost of the factors the iteration starts from is a by-product
+    of that kernel's quotient (k_fused<H step, COST>; reduce1d_div, cuda/matrix.cu:578-640).  Iteration 26 is the
+    first check: it reports the cost after 25 iterations.  (2100 rows: the rows of W are split over work items.)"""
+    monkeypatch.setenv("NMF_UMMA_FUSE", "2")
+    W, H, X = rand_problem(*shape, seed=21)
+    _, _, _, cost25 = oracle.update_div(W, H, X, 0.0, 25, "exact", acc64=True)
+    Wo, Ho, _, _ = oracle.update_div(W, H, X, 0.0, 26, "exact", acc64=True)
+    Wd, Hd = W.copy(order="F"), H.copy(order="F")
+    res = api.update_div(Wd, Hd, X, 1e-12, 26)
+    assert res.iterations == 26 and res.converged == 0
+    assert abs(res.cost - cost25) / cost25 < 1e-5
+    assert max_rel(Wd, Wo) < 1e-4 and max_rel(Hd, Ho) < 1e-4
+
+
+@pytest.mark.parametrize("graph", [True, False])
+def test_fused_check_iteration_restores_h_on_convergence(api, oracle, graph, monkeypatch):
+    """the fused H step of a check iteration has already rewritten H when the cost says "converged": the run hands
+    back the H it saved, i.e. the factors the oracle stops with"""
+    monkeypatch.setenv("NMF_UMMA_FUSE", "2")
+    rng = np.random.RandomState(5)
+    X = np.asfortranarray((rng.rand(300, 8) @ rng.rand(8, 700)).astype(np.float32))
+    W, H, _ = rand_problem(300, 700, 64, seed=6)
+    Wo, Ho, it, cost = oracle.update_div(W, H, X, 0.5, 400, "exact", acc64=True)
+    Wd, Hd = W.copy(order="F"), H.copy(order="F")
+    res = api.update_div(Wd, Hd, X, 0.5, 400, opt=api.options(use_graph=graph))
+    assert res.converged == 1 and res.iterations == it and it % 25 == 0
+    assert abs(res.cost - cost) / cost < 1e-4
+    assert max_rel(Wd, Wo) < 1e-3 and max_rel(Hd, Ho) < 1e-3
+    # and the session's TF32 pair of H was rebuilt from the restored H: a further iteration from the result agrees
+    W2, H2, _, _ = oracle.update_div(Wd, Hd, X, 0.0, 1, "exact", acc64=True)
+    We, He = Wd.copy(order="F"), Hd.copy(order="F")
+    api.update_div(We, He, X, 0.0, 1)
+    assert max_rel(We, W2) < 1e-4 and max_rel(He, H2) < 1e-4
 
 
 @pytest.mark.parametrize("chunk", [1, 4, 16])
@@ -205,9 +249,22 @@ def test_chunk_period_bounds_truncation_bias(api, chunk, monkeypatch):
 # ---------------------------------------------------------------------------------------------
 # update_div end to end
 # ---------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("engine", ENGINES)
-def test_c1_exact_100_iterations(api, oracle, c1, engine):
+# ENGINES x the tcgen05 engine's two paths: "tcgen05" = its default (fused half-iterations where the shape allows,
+# i.e. C1 and C2), "tcgen05-2k" = NMF_UMMA_FUSE=0, the two-kernel path (what K > 256 or K_v not a multiple of 64 take)
+PATHS = ENGINES + ["tcgen05-2k"]
+
+
+def engine_path(path, monkeypatch):
+    if path == "tcgen05-2k":
+        monkeypatch.setenv("NMF_UMMA_FUSE", "0")
+        return "tcgen05"
+    return path
+
+
+@pytest.mark.parametrize("engine", PATHS)
+def test_c1_exact_100_iterations(api, oracle, c1, engine, monkeypatch):
     """BASELINE config C1, exact semantics: the north-star tolerance."""
+    engine = engine_path(engine, monkeypatch)
     W = c1["W"].copy(order="F"); H = c1["H"].copy(order="F")
     res = api.update_div(W, H, c1["X"], 0.0, 100, opt=api.options(engine=engine))
     assert res.iterations == 100
@@ -218,9 +275,10 @@ def test_c1_exact_100_iterations(api, oracle, c1, engine):
     assert abs(cost - 105982.05) / 105982.05 < 1e-5                 # BASELINE.md known answer
 
 
-@pytest.mark.parametrize("engine", ENGINES)
-def test_c1_refcompat_matches_reference_golden(api, oracle, c1, engine):
+@pytest.mark.parametrize("engine", PATHS)
+def test_c1_refcompat_matches_reference_golden(api, oracle, c1, engine, monkeypatch):
     """200 iterations, thresh 0 (cuda/nmf.cu:10-11) == the reference's Wtest.bin / Htest.bin"""
+    engine = engine_path(engine, monkeypatch)
     W = c1["W"].copy(order="F"); H = c1["H"].copy(order="F")
     res = api.update_div(W, H, c1["X"], 0.0, 200, opt=api.options(semantics="refcompat", engine=engine))
     assert res.iterations == 200
@@ -230,9 +288,10 @@ def test_c1_refcompat_matches_reference_golden(api, oracle, c1, engine):
     assert fro_rel(W, c1["Wtest"]) <= 2e-3 and fro_rel(H, c1["Htest"]) <= 2e-3
 
 
-@pytest.mark.parametrize("engine", ENGINES)
-def test_c2_shape_small_k(api, oracle, engine):
+@pytest.mark.parametrize("engine", PATHS)
+def test_c2_shape_small_k(api, oracle, engine, monkeypatch):
     """ISMIR shape family (M=513, K=40: ragged rows, K padded to 64), fewer columns/iterations"""
+    engine = engine_path(engine, monkeypatch)
     W, H, X = rand_problem(513, 2000, 40, seed=1)
     Wd = W.copy(order="F"); Hd = H.copy(order="F")
     api.update_div(Wd, Hd, X, 0.0, 30, opt=api.options(engine=engine))
@@ -265,8 +324,12 @@ def test_convergence_threshold_and_cost(api, oracle, engine):
     assert abs(res.cost - cost) / cost < 1e-4
 
 
-def test_t10_and_graph_vs_eager(api, c1):
-    """per-phase timers are filled; graph replay and eager launches give identical bits"""
+@pytest.mark.parametrize("fuse", ["0", "1"])
+def test_t10_and_graph_vs_eager(api, c1, fuse, monkeypatch):
+    """per-phase timers are filled; graph replay and eager launches give identical bits.  With the fused
+    half-iterations (default) the W*H GEMM and the quotient run inside the k_fused launches charged to t[3], and
+    t[0] stays 0 unless an iteration needs the cost from the two-kernel path (include/nmf.h)."""
+    monkeypatch.setenv("NMF_UMMA_FUSE", fuse)
     W0, H0, X = c1["W"][:, :64], c1["H"][:64], c1["X"]
     Wa = W0.copy(order="F"); Ha = H0.copy(order="F")
     Wb = W0.copy(order="F"); Hb = H0.copy(order="F")
@@ -274,7 +337,8 @@ def test_t10_and_graph_vs_eager(api, c1):
     api.update_div(Wa, Ha, X, 0.0, 10, t=t)                       # timed => eager
     api.update_div(Wb, Hb, X, 0.0, 10)                            # graph
     assert np.array_equal(Wa, Wb) and np.array_equal(Ha, Hb)
-    assert t[0] > 0 and t[2] > 0 and t[3] > 0 and t[5] > 0 and t[9] >= t[0] + t[3]
+    assert t[2] > 0 and t[3] > 0 and t[5] > 0 and t[9] >= t[0] + t[3]
+    assert (t[0] > 0) if fuse == "0" else (t[0] == 0)
 
 
 def test_full_size_properties(api):
