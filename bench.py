@@ -163,7 +163,9 @@ def main():
 
     n_off, n_loc = shard(N, rank, world)
     opt = api.options(engine=args.engine, device=local)
+    free0 = torch.cuda.mem_get_info()[0]
     sess = api.Session(M, n_loc, K, n_offset=n_off, n_global=N, opt=opt)
+    hbm_resident = int(free0 - torch.cuda.mem_get_info()[0])  # the session's device buffers (X, W, H + pairs, partials; no quotient when fused)
 
     def join(session):
         """fresh ncclUniqueId from rank 0, broadcast over torch.distributed, then ncclCommInitRank"""
@@ -280,6 +282,7 @@ def main():
                 "data": "synthetic",
                 "config": {"workload": desc, "M": M, "N": N, "K": K, "columns_per_gpu": n_loc,
                            "parallelism": f"column-sharded x{world}", "engine": args.engine,
+                           "hbm_resident_bytes_per_gpu": hbm_resident,
                            "l2": "inputs (X alone >= 2 GB per GPU) far exceed the 126 MB L2; no flush needed"},
                 "effective_tflops": flop_iter / (ms_per_step * 1e-3) / 1e12,
                 "gpu_launches": int(launches), "e2e": e2e, "roofline": roofline, "clocks": clocks}

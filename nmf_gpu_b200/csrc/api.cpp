@@ -299,6 +299,7 @@ int nmf_dbg_quotient(const float* W, const float* H, const float* X, float* Y, d
                      int M, int N, int K, const nmf_options* opt) {
     return guarded([&] {
         with_session(W, H, X, M, N, K, opt, [&](nmf_session_impl& s) {
+            session_need_quotient(s);        // a session whose half-iterations are both fused keeps no quotient buffer
             iteration_head(s, cost != nullptr, nullptr);
             const Dims& d = s.d;
             std::vector<float> a((size_t)d.Mv * d.Nv), b;

@@ -4,6 +4,7 @@
 
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <vector>
@@ -96,7 +97,10 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
             s->n_cost_partials = simt_cost_partial_count(d);
             s->nsplit = 1;
         } else {
-            s->Y = dalloc<float>(d.szXa());     // stored once as fp32; the GEMMs that consume it split it in the SM
+            // stored once as fp32; the GEMMs that consume it split it in the SM.  Not needed at all when both
+            // half-iterations are fused (NMF_KEEP_QUOTIENT=1 allocates it anyway)
+            const char* keep = std::getenv("NMF_KEEP_QUOTIENT");
+            if (!umma::fused_both_wanted(d, opt.tf32_passes) || (keep && std::atoi(keep) != 0)) s->Y = dalloc<float>(d.szXa());
             s->Whi = dalloc<float>(d.szW()); s->Wlo = dalloc<float>(d.szW());
             s->Hhi = dalloc<float>(d.szHa()); s->Hlo = dalloc<float>(d.szHa());
             s->n_cost_partials = umma::cost_partial_count(d);
@@ -115,6 +119,18 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
         throw;
     }
     return s;
+}
+
+void session_need_quotient(nmf_session_impl& s) {
+    if (s.Y) return;
+    CUDA_CHECK(cudaSetDevice(s.device));
+    s.Y = dalloc<float>(s.d.szXa());
+    if (s.plan) {                     // its tensor maps and kernel parameters hold the buffer's address
+        umma::plan_destroy(s.plan); s.plan = nullptr;
+        s.plan = umma::plan_create(s);
+        if (s.g_full) { cudaGraphExecDestroy(s.g_full); s.g_full = nullptr; }
+        if (s.g_rest) { cudaGraphExecDestroy(s.g_rest); s.g_rest = nullptr; }
+    }
 }
 
 // After any change of W or H masters: refresh the TF32 splits the tcgen05 engine reads.
@@ -334,13 +350,16 @@ static void build_graphs(nmf_session_impl& s) {
     CUDA_CHECK(cudaGraphDestroy(g));
     s.launches_head = c1 - c0;
     s.launches_full = s.launches - c0;
-    c0 = s.launches;
-    CUDA_CHECK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
-    iteration_rest(s, nullptr);
-    CUDA_CHECK(cudaStreamEndCapture(s.stream, &g));
-    CUDA_CHECK(cudaGraphInstantiate(&s.g_rest, g, 0));
-    CUDA_CHECK(cudaGraphDestroy(g));
-    s.launches_rest = s.launches - c0;
+    s.launches_rest = 0;
+    if (!fused_check_enabled(s)) {      // check iterations of the two-kernel path: head (eager, with the cost) + this graph
+        c0 = s.launches;
+        CUDA_CHECK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
+        iteration_rest(s, nullptr);
+        CUDA_CHECK(cudaStreamEndCapture(s.stream, &g));
+        CUDA_CHECK(cudaGraphInstantiate(&s.g_rest, g, 0));
+        CUDA_CHECK(cudaGraphDestroy(g));
+        s.launches_rest = s.launches - c0;
+    }
     s.launches -= s.launches_full + s.launches_rest;    // capture launched nothing
 }
 

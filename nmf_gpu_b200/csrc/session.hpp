@@ -16,8 +16,10 @@ struct nmf_session_impl {
 
     // fp32 masters (column-major, ld = Mv / Kv)
     float *W = nullptr, *H = nullptr, *X = nullptr;
-    // quotient Y = X ./ max(WH,EPS): SIMT engine keeps one fp32 copy, tcgen05 engine the TF32 split
-    float *Y = nullptr;                           // quotient X ./ max(W*H,EPS), stored once as fp32
+    // quotient Y = X ./ max(W*H,EPS), stored once as fp32 by the two-kernel path.  nullptr when both half-iterations
+    // run fused (the quotient then never leaves the SM): the M x N buffer is not even allocated, which halves the
+    // footprint of a session (session_need_quotient allocates it for the debug entry points that read it)
+    float *Y = nullptr;
     // TF32 splits of the small operands (tcgen05 engine)
     float *Whi = nullptr, *Wlo = nullptr, *Hhi = nullptr, *Hlo = nullptr;
     // sums and the packed allreduce buffer [ numerator P (Mv*Kv) | sumH (Kv) ]
@@ -54,6 +56,8 @@ void iteration_head(nmf_session_impl& s, bool with_cost, PhaseTimer* pt);   // c
 void iteration_rest(nmf_session_impl& s, PhaseTimer* pt);                   // H update; rowsum; quotient; numerator; [allreduce]; W update
 void iteration_full(nmf_session_impl& s, PhaseTimer* pt);                   // one whole iteration without a cost (fused H step when enabled)
 
+void session_need_quotient(nmf_session_impl& s);   // allocate Y (and re-plan) if the session was created without it
+
 // NCCL (dist.cpp)
 int  nccl_unique_id(void* id128);
 void nccl_join(nmf_session_impl& s, int rank, int nranks, const void* id128);
@@ -80,6 +84,7 @@ bool  fused_h_enabled(const nmf_session_impl& s);
 int   fused_h(nmf_session_impl& s, bool with_cost = false);   // returns the kernels launched (2 when the rows of W are split)
 int   fused_h_splits(const Dims& d, int passes);
 int   fused_cost_partial_count(const Dims& d, int passes);
+bool  fused_both_wanted(const Dims& d, int passes);
 // raw contraction for descriptor bring-up (nmf_dbg_gemm)
 void  dbg_gemm(int which, const float* dA, const float* dB, float* dC, int M, int N, int K, int passes,
                cudaStream_t st);

@@ -189,6 +189,25 @@ def test_fused_iterations_c1(api, oracle, c1, graph, monkeypatch):
     assert res.iterations == 100
     assert max_rel(Wd, Wo) < 1e-4 and max_rel(Hd, Ho) < 1e-4
     assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
+    # the closing cost comes from the quotient kernel run for its cost only (no quotient buffer in a fully fused session)
+    assert abs(res.cost - cost) / cost < 1e-5
+
+
+def test_fully_fused_session_keeps_no_quotient_buffer(api, oracle, monkeypatch):
+    """both half-iterations fused: the M x N quotient buffer is not allocated; NMF_KEEP_QUOTIENT=1 allocates it anyway
+    and must not change a bit; the debug entry point that returns the quotient allocates it on demand"""
+    W, H, X = rand_problem(600, 1300, 128, seed=4)
+    out = []
+    for keep in ("0", "1"):
+        monkeypatch.setenv("NMF_KEEP_QUOTIENT", keep)
+        Wd, Hd = W.copy(order="F"), H.copy(order="F")
+        res = api.update_div(Wd, Hd, X, 1e-12, 30)
+        out.append((Wd, Hd, res.cost))
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1]) and out[0][2] == out[1][2]
+    monkeypatch.setenv("NMF_KEEP_QUOTIENT", "0")
+    Y, cost = api.dbg_quotient(W, H, X, api.options(), with_cost=True)
+    co = oracle.kl(W, H, X)
+    assert max_rel(Y, oracle.quotient(W, H, X, acc64=True)) < 5e-6 and abs(cost - co) / co < 1e-5
 
 
 @pytest.mark.parametrize("shape", [(300, 700, 64), (600, 1300, 256), (520, 3000, 128), (2100, 600, 64)])
