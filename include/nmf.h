@@ -149,8 +149,9 @@ int nmf_session_run(nmf_session *s, float CONVERGE_THRESH, int max_iter, double 
 int nmf_session_cost(nmf_session *s, double *cost);
 
 /* Which half-iterations this session runs as ONE kernel (the quotient never leaves the SM): bit 0 the W
- * step, bit 1 the H step; 0 for the two-kernel path (small problems, K not a multiple of 64 or > 256,
- * NMF_UMMA_FUSE=0).  Informational: results are within the same tolerance either way. */
+ * step, bit 1 the H step; 0 for the two-kernel path (padded K not a multiple of 64 or > 256, fewer than
+ * 129 rows / columns, NMF_UMMA_FUSE=0).  Informational: results are within the same tolerance either
+ * way.  A session with both bits set allocates no M x N quotient buffer. */
 int nmf_session_fused_steps(const nmf_session *s);
 
 /* ------------------------------------------------------------------------------------------

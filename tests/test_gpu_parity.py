@@ -164,17 +164,26 @@ def test_fused_h_step(api, oracle, shape, mode, monkeypatch):
     assert max_rel(H1, H0) < 1e-5
 
 
-@pytest.mark.parametrize("nw", ["2", "4"])
-def test_fused_worker_warp_variants(api, oracle, nw, monkeypatch):
-    """K <= 128 runs 4 worker warps per TMEM lane quadrant by default (the quotient bounds the kernel there), K > 128
-    two; NMF_UMMA_FUSE_NW forces either on a K = 128 problem"""
-    monkeypatch.setenv("NMF_UMMA_FUSE", "2")
+@pytest.mark.parametrize("nw,bn", [("2", "256"), ("4", "256"), ("4", "128")])
+@pytest.mark.parametrize("shape", [(700, 1500, 128), (513, 3000, 40), (2100, 900, 64)])
+def test_fused_kernel_variants(api, oracle, nw, bn, shape, monkeypatch):
+    """K <= 128 runs 4 worker warps per TMEM lane quadrant (the quotient bounds the kernel there) and two double-buffered
+    128-wide S tiles (the S GEMM of the next tile overlaps the quotient of the current one) by default, K > 128 two
+    worker warps and one 256-wide S tile; NMF_UMMA_FUSE_NW / NMF_UMMA_FUSE_BN force each combination.  Half-steps
+    and 30 whole iterations (ragged last tiles, several tiles and work items per CTA pair, cost checks)."""
     monkeypatch.setenv("NMF_UMMA_FUSE_NW", nw)
-    W, H, X = rand_problem(700, 1500, 128, seed=9)
+    monkeypatch.setenv("NMF_UMMA_FUSE_BN", bn)
+    W, H, X = rand_problem(*shape, seed=9)
     H1 = api.dbg_h_step(W, H, X, api.options())
     assert max_rel(H1, oracle.h_step(W, H, X, "exact", acc64=True)) < 2e-5
     W1 = api.dbg_w_step(W, H, X, api.options())
     assert max_rel(W1, oracle.w_step(W, H, X, "exact", acc64=True)) < 2e-5
+    Wo, Ho, _, cost = oracle.update_div(W, H, X, 0.0, 30, "exact", acc64=True)
+    Wd, Hd = W.copy(order="F"), H.copy(order="F")
+    res = api.update_div(Wd, Hd, X, 1e-12, 30)
+    assert res.iterations == 30
+    assert max_rel(Wd, Wo) < 1e-4 and max_rel(Hd, Ho) < 1e-4
+    assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
 
 
 @pytest.mark.parametrize("graph", [True, False])
