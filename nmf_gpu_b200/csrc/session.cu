@@ -109,7 +109,8 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
             if (s->nsplit > 1) s->Psplit = dalloc<float>((size_t)s->nsplit * d.szW());
             s->hsplit = umma::updh_splits(d);
             s->fhsplit = umma::fused_h_splits(d, opt.tf32_passes);
-            if (std::max(s->hsplit, s->fhsplit) > 1) s->Hpart = dalloc<float>((size_t)std::max(s->hsplit, s->fhsplit) * d.szHa());
+            if (std::max(s->hsplit, s->fhsplit) > 1 || umma::fused_h_needs_part(d, opt.tf32_passes))
+                s->Hpart = dalloc<float>((size_t)std::max(s->hsplit, s->fhsplit) * d.szHa());
             s->plan = umma::plan_create(*s);
         }
         s->cost_partials = dalloc<double>(std::max(1, std::max(s->n_cost_partials, s->n_cost_partials_fused)));
