@@ -424,7 +424,13 @@ void session_run(nmf_session_impl& s, float thresh, int max_iter, double t[10], 
         if (thresh > 0.0f && done % every == 0 && rel < (double)thresh) converged = 1;
     }
     CUDA_CHECK(cudaEventRecord(e1, s.stream));
-    CUDA_CHECK(cudaStreamSynchronize(s.stream));
+    {
+        const cudaError_t e = cudaStreamSynchronize(s.stream);
+        if (e != cudaSuccess && s.opt.engine == NMF_ENGINE_TCGEN05 && umma::protocol_error(s))
+            NMF_CHECK(false, std::string("kernel trapped: bounded mbarrier wait ") + std::to_string(umma::protocol_error(s)) +
+                             " gave up (" + cudaGetErrorString(e) + ")");
+        CUDA_CHECK(e);
+    }
     float ms = 0; CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
     CUDA_CHECK(cudaEventDestroy(e0)); CUDA_CHECK(cudaEventDestroy(e1));
     if (pt) {

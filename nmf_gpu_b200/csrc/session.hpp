@@ -85,6 +85,7 @@ int   fused_h(nmf_session_impl& s, bool with_cost = false);   // returns the ker
 int   fused_h_splits(const Dims& d, int passes);
 int   fused_cost_partial_count(const Dims& d, int passes);
 bool  fused_both_wanted(const Dims& d, int passes);
+unsigned int protocol_error(const nmf_session_impl& s);
 bool  fused_h_needs_part(const Dims& d, int passes);   // the fused H step writes partial sums (row split or deferred update)
 // raw contraction for descriptor bring-up (nmf_dbg_gemm)
 void  dbg_gemm(int which, const float* dA, const float* dB, float* dC, int M, int N, int K, int passes,

@@ -50,7 +50,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, unsigned int* err_flag, unsigned int code) {
     uint32_t tries = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (++tries > (1u << 24)) {
+        if (++tries > (1u << 22)) {
             if (err_flag) atomicExch(err_flag, code);
             __threadfence_system();
             __trap();
@@ -209,7 +209,7 @@ __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t pa
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity, unsigned int* err_flag, unsigned int code) {
     uint32_t tries = 0;
     while (!mbar_try_wait_cluster(bar, parity)) {
-        if (++tries > (1u << 24)) {
+        if (++tries > (1u << 22)) {
             if (err_flag) atomicExch(err_flag, code);
             __threadfence_system();
             __trap();
@@ -260,7 +260,7 @@ __device__ __forceinline__ bool mbar_try_wait_a(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity, unsigned int* err_flag, unsigned int code) {
     uint32_t tries = 0;
     while (!mbar_try_wait_a(bar, parity)) {
-        if (++tries > (1u << 24)) {
+        if (++tries > (1u << 22)) {
             if (err_flag) atomicExch(err_flag, code);
             __threadfence_system();
             __trap();

@@ -22,8 +22,8 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     rank, world = dist.get_rank(), dist.get_world_size()
-    # every rank owns columns (shards are 256-column blocks); K a multiple of 64 so that NMF_UMMA_FUSE=2 runs the
-    # fused half-iteration kernels on every rank (the default only fuses large problems)
+    # every rank owns columns (shards are 256-column blocks); K a multiple of 64 so that the fused half-iteration
+    # kernels run on every rank (NMF_UMMA_FUSE=0 takes the two-kernel path instead)
     M, N, K, iters = 1024, max(4096, 1024 * world) + 300, 128, 30
     W, H, X = rand_problem(M, N, K, seed=11)
     out = {}

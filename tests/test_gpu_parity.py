@@ -164,13 +164,14 @@ def test_fused_h_step(api, oracle, shape, mode, monkeypatch):
     assert max_rel(H1, H0) < 1e-5
 
 
-@pytest.mark.parametrize("nw,bn", [("2", "256"), ("4", "256"), ("4", "128")])
-@pytest.mark.parametrize("shape", [(700, 1500, 128), (513, 3000, 40), (2100, 900, 64)])
+@pytest.mark.parametrize("nw,bn", [("2", "256"), ("2", "128"), ("4", "256"), ("4", "128")])
+@pytest.mark.parametrize("shape", [(700, 1500, 128), (513, 3000, 40), (2100, 900, 64), (600, 1300, 256)])
 def test_fused_kernel_variants(api, oracle, nw, bn, shape, monkeypatch):
-    """K <= 128 runs 4 worker warps per TMEM lane quadrant (the quotient bounds the kernel there) and two double-buffered
-    128-wide S tiles (the S GEMM of the next tile overlaps the quotient of the current one) by default, K > 128 two
-    worker warps and one 256-wide S tile; NMF_UMMA_FUSE_NW / NMF_UMMA_FUSE_BN force each combination.  Half-steps
-    and 30 whole iterations (ragged last tiles, several tiles and work items per CTA pair, cost checks)."""
+    """K <= 128 runs 4 worker warps per TMEM lane quadrant (the quotient bounds the kernel there), K > 128 two; both use
+    two double-buffered 128-wide S tiles by default (the S GEMM of the next tile overlaps the quotient of the current
+    one) instead of one 256-wide tile; NMF_UMMA_FUSE_NW / NMF_UMMA_FUSE_BN force each combination (4 warps need
+    K <= 128).  Half-steps and 30 whole iterations (ragged last tiles, several tiles and work items per CTA pair,
+    cost checks)."""
     monkeypatch.setenv("NMF_UMMA_FUSE_NW", nw)
     monkeypatch.setenv("NMF_UMMA_FUSE_BN", bn)
     W, H, X = rand_problem(*shape, seed=9)
