@@ -1,6 +1,7 @@
 """update_div on several GPUs from ONE process (NMF_NUM_GPUS=g: a host thread per GPU inside the library,
 README-style call, no launcher): must reproduce the single-GPU result up to reduction order.
-    python tests/multi_gpu_update_div.py [g]        (needs g visible GPUs; prints one PARITY line)"""
+    python tests/multi_gpu_update_div.py [g [K]]    (needs g visible GPUs; prints one PARITY line; K = 96 takes the
+two-kernel path, a multiple of 64 such as 128 the fused half-iterations)"""
 import json
 import os
 import sys
@@ -15,7 +16,7 @@ from util import max_rel, rand_problem
 
 def main():
     g = int(sys.argv[1]) if len(sys.argv) > 1 else 2
-    M, N, K, iters = 1024, max(4096, 1024 * g) + 300, 96, 30
+    M, N, K, iters = 1024, max(4096, 1024 * g) + 300, (int(sys.argv[2]) if len(sys.argv) > 2 else 96), 30
     W, H, X = rand_problem(M, N, K, seed=11)
     out = {}
     for mode in ("exact", "refcompat"):
@@ -30,7 +31,7 @@ def main():
         out[mode] = dict(W=max_rel(Wg, W1), H=max_rel(Hg, H1), iters=(rg.iterations, r1.iterations),
                          cost_rel=abs(rg.cost - r1.cost) / abs(r1.cost), allreduce_s=float(t[7]))
     os.environ["NMF_NUM_GPUS"] = "1"
-    print("PARITY " + json.dumps(dict(gpus=g, **out)), flush=True)
+    print("PARITY " + json.dumps(dict(gpus=g, K=K, **out)), flush=True)
     ok = all(v["W"] < 2e-5 and v["H"] < 2e-5 and v["cost_rel"] < 1e-5 and v["iters"][0] == v["iters"][1]
              for k, v in out.items() if k == "exact") and out["refcompat"]["cost_rel"] < 1e-5
     sys.exit(0 if ok else 1)
