@@ -187,6 +187,23 @@ def test_fused_kernel_variants(api, oracle, nw, bn, shape, monkeypatch):
     assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
 
 
+@pytest.mark.parametrize("env", [{"NMF_UMMA_FH_DEFER": "1"}, {"NMF_UMMA_FHSPLIT": "1"}, {"NMF_UMMA_FHSPLIT": "3"},
+                                 {"NMF_UMMA_FHSPLIT": "64"}])
+def test_fused_h_step_split_switches(api, oracle, env, monkeypatch):
+    """the fused H step with its tuning switches forced: update left to k_update_h, no row split, 3 splits, and as many
+    splits as there are 256-row tiles (the request is clamped)"""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    W, H, X = rand_problem(1100, 900, 128, seed=31)
+    H1 = api.dbg_h_step(W, H, X, api.options())
+    assert max_rel(H1, oracle.h_step(W, H, X, "exact", acc64=True)) < 2e-5
+    Wo, Ho, _, cost = oracle.update_div(W, H, X, 0.0, 26, "exact", acc64=True)
+    Wd, Hd = W.copy(order="F"), H.copy(order="F")
+    res = api.update_div(Wd, Hd, X, 1e-12, 26)
+    assert res.iterations == 26
+    assert max_rel(Wd, Wo) < 1e-4 and max_rel(Hd, Ho) < 1e-4
+
+
 @pytest.mark.parametrize("graph", [True, False])
 def test_fused_iterations_c1(api, oracle, c1, graph, monkeypatch):
     """100 iterations of C1 with both half-iterations fused, cost checks every 25 (the COST instantiation of the
