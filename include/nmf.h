@@ -66,7 +66,10 @@ void destroy_matrix(matrix *A);
  *                     t[2] row/column sums, t[3] W'Y / YH' GEMMs with the fused divide+multiply,
  *                     t[4] 0 (fused into t[3]), t[5] W multiply/update kernel, t[6] cost read-back
  *                     and convergence test, t[7] allreduce, t[8] H2D/D2H + allocation + setup,
- *                     t[9] total wall time of the call
+ *                     t[9] total wall time of the call.  Where a half-iteration runs as ONE fused
+ *                     kernel (the default whenever the padded K is a multiple of 64 and <= 256) its
+ *                     W*H GEMM, quotient and second GEMM are all charged to t[3] and t[0] stays 0;
+ *                     on check iterations t[6] also holds the copy that saves H
  *   verbose         : 1 prints the cost every 25 iterations
  * Semantics (exact | refcompat) and GPU selection come from the environment: NMF_SEMANTICS,
  * NMF_DEVICE, NMF_ENGINE; defaults: exact, device 0, tcgen05 engine.
