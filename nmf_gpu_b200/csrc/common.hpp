@@ -97,8 +97,12 @@ void launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nspli
 // out[e] = sum_s P[s][e] in split order (multi-GPU: fold the local splits before the allreduce).
 void launch_fold_splits(const float* P, int nsplit, size_t split_stride, float* out, size_t n, cudaStream_t st);
 // H <- H .* ((sum of the nsplit partial W'*Y) ./ max(sumW,EPS)), plus the TF32 pair of the new H
-void launch_update_h(float* H, float* Hhi, float* Hlo, const float* P, int nsplit, size_t split_stride,
-                     const float* sumW, const Dims& d, cudaStream_t st);
+// With `rowsum_partials` (rowsum_partial_count(d) * d.Kv floats) and Kv in {64, 128, 256} the kernel also emits per-block
+// partial row sums of the new H; returns the number of blocks that wrote them (0: none, run launch_rowsum instead).
+int  launch_update_h(float* H, float* Hhi, float* Hlo, const float* P, int nsplit, size_t split_stride,
+                     const float* sumW, const Dims& d, cudaStream_t st, float* rowsum_partials = nullptr);
+// sumH = ordered fold of the `nblocks` partial row sums launch_update_h left in `partials`
+void launch_rowsum_finish2(const float* partials, float* sumH, int nblocks, const Dims& d, cudaStream_t st);
 
 // cost = sum of `n` double partials (ordered).
 void launch_sum_partials(const double* partials, int n, double* out, cudaStream_t st);

@@ -185,9 +185,15 @@ __global__ void __launch_bounds__(256) k_update_w(float* __restrict__ W, float* 
 // H update from split partial sums of W'*Y (small problems: the H GEMM is split over the rows of W so
 // that it fills the SMs): H <- H .* ((sum_s P[s]) ./ max(sumW,EPS)), ordered sum, emits the TF32 pair.
 // One thread per 4 consecutive k of one column (float4; Kv is a multiple of 32).
+// ROWSUM (Kv in {64, 128, 256}: every thread keeps the same 4 rows k over its grid-stride loop): the block also emits
+// its partial row sums of the NEW H, rs_partials[block][k] (refcompat: only the columns of the reference's subsample),
+// so that the W half needs no pass of its own over H: k_rowsum_finish2 folds the blocks in a fixed order.
+template <bool ROWSUM>
 __global__ void __launch_bounds__(256) k_update_h(float* __restrict__ H, float* __restrict__ Hhi, float* __restrict__ Hlo,
                                                   const float* __restrict__ P, int nsplit, size_t split_stride,
-                                                  const float* __restrict__ sumW, int Kv, size_t total4) {
+                                                  const float* __restrict__ sumW, int Kv, size_t total4,
+                                                  float* __restrict__ rs_partials, long long n_offset, int refcompat) {
+    float4 rs = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
         const size_t e = i * 4;
         const int k = (int)(e % (size_t)Kv);
@@ -209,6 +215,37 @@ __global__ void __launch_bounds__(256) k_update_h(float* __restrict__ H, float* 
             *reinterpret_cast<float4*>(Hhi + e) = hi;
             *reinterpret_cast<float4*>(Hlo + e) = lo;
         }
+        if (ROWSUM && (!refcompat || ref_sum_mask(n_offset + (long long)(e / (size_t)Kv)))) {
+            rs.x += h.x; rs.y += h.y; rs.z += h.z; rs.w += h.w;
+        }
+    }
+    if (ROWSUM) {
+        // threads tid, tid + Kv/4, tid + 2 Kv/4, .. own the same rows (256 and the grid stride are multiples of Kv/4)
+        __shared__ float4 sm[256];
+        sm[threadIdx.x] = rs;
+        __syncthreads();
+        const int k4n = Kv >> 2;
+        if ((int)threadIdx.x < k4n) {
+            float4 t = sm[threadIdx.x];
+            for (int j = (int)threadIdx.x + k4n; j < 256; j += k4n) { const float4 v = sm[j]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
+            *reinterpret_cast<float4*>(rs_partials + (size_t)blockIdx.x * Kv + 4 * threadIdx.x) = t;
+        }
+    }
+}
+
+// ordered fold of per-block partial row sums: block = 32 rows k x 32 groups; group g sums blocks g, g + 32, ..
+__global__ void __launch_bounds__(1024) k_rowsum_finish2(const float* __restrict__ partials, float* __restrict__ sumH, int Kv, int nblocks) {
+    __shared__ float sm[32][33];
+    const int k = blockIdx.x * 32 + threadIdx.x;
+    float s = 0.0f;
+    if (k < Kv) for (int c = threadIdx.y; c < nblocks; c += 32) s += partials[(size_t)c * Kv + k];
+    sm[threadIdx.y][threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.y == 0 && k < Kv) {
+        float t = 0.0f;
+        #pragma unroll
+        for (int j = 0; j < 32; ++j) t += sm[j][threadIdx.x];
+        sumH[k] = t;
     }
 }
 
@@ -288,10 +325,14 @@ void launch_colsum(const float* W, float* sumW, const Dims& d, cudaStream_t st) 
     CUDA_CHECK_LAUNCH();
 }
 
-int rowsum_partial_count(const Dims& d) { return (d.Nv + kRowsumChunk - 1) / kRowsumChunk; }
+int rowsum_partial_count(const Dims& d) {
+    // enough for either producer: 512-column chunks (k_rowsum_partial) or the blocks of k_update_h<ROWSUM>
+    const int chunks = (d.Nv + kRowsumChunk - 1) / kRowsumChunk;
+    return std::max(chunks, grid_for((size_t)d.Kv * d.Nv / 4, 256));
+}
 
 void launch_rowsum(const float* H, float* partials, float* sumH, const Dims& d, cudaStream_t st) {
-    const int nch = rowsum_partial_count(d);
+    const int nch = (d.Nv + kRowsumChunk - 1) / kRowsumChunk;
     dim3 grid((d.Kv + 31) / 32, nch), block(32, 8);
     k_rowsum_partial<<<grid, block, 0, st>>>(H, partials, d.Kv, d.Nv, d.n_offset, d.refcompat);
     CUDA_CHECK_LAUNCH();
@@ -306,10 +347,19 @@ void launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nspli
     CUDA_CHECK_LAUNCH();
 }
 
-void launch_update_h(float* H, float* Hhi, float* Hlo, const float* P, int nsplit, size_t split_stride,
-                     const float* sumW, const Dims& d, cudaStream_t st) {
+int launch_update_h(float* H, float* Hhi, float* Hlo, const float* P, int nsplit, size_t split_stride,
+                    const float* sumW, const Dims& d, cudaStream_t st, float* rowsum_partials) {
     const size_t total4 = (size_t)d.Kv * d.Nv / 4;
-    k_update_h<<<grid_for(total4, 256), 256, 0, st>>>(H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4);
+    const int grid = grid_for(total4, 256);
+    const bool rowsum = rowsum_partials != nullptr && (d.Kv == 64 || d.Kv == 128 || d.Kv == 256);
+    if (rowsum) k_update_h<true><<<grid, 256, 0, st>>>(H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4, rowsum_partials, d.n_offset, d.refcompat);
+    else        k_update_h<false><<<grid, 256, 0, st>>>(H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4, nullptr, 0, 0);
+    CUDA_CHECK_LAUNCH();
+    return rowsum ? grid : 0;
+}
+
+void launch_rowsum_finish2(const float* partials, float* sumH, int nblocks, const Dims& d, cudaStream_t st) {
+    k_rowsum_finish2<<<(d.Kv + 31) / 32, dim3(32, 32), 0, st>>>(partials, sumH, d.Kv, nblocks);
     CUDA_CHECK_LAUNCH();
 }
 

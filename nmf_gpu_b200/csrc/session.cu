@@ -267,6 +267,7 @@ static void iteration_head_fused_cost(nmf_session_impl& s, PhaseTimer* pt) {
     });
 }
 static void restore_h(nmf_session_impl& s) {
+    s.rowsum_blocks = 0;              // partial row sums the abandoned H step may have left belong to the H being discarded
     CUDA_CHECK(cudaMemcpyAsync(s.H, s.Hbak, s.d.szHa() * 4, cudaMemcpyDeviceToDevice, s.stream));
     launch_split_tf32(s.H, s.Hhi, s.Hlo, s.d.szH(), s.stream); count_launches(s, 1);
 }
@@ -297,7 +298,12 @@ void iteration_full(nmf_session_impl& s, PhaseTimer* pt) {
 static void w_half(nmf_session_impl& s, PhaseTimer* pt) {
     const Dims& d = s.d;
     // sum rows of H (nmf.cu:164) into the packed buffer's tail
-    PHASE(pt, PH_SUMS, { launch_rowsum(s.H, s.rowsum_partials, s.sumH, d, s.stream); count_launches(s, 2); });
+    // (when the H update ran as its own kernel it left per-block partial sums of the new H: only the fold remains)
+    PHASE(pt, PH_SUMS, {
+        if (s.rowsum_blocks > 0) { launch_rowsum_finish2(s.rowsum_partials, s.sumH, s.rowsum_blocks, d, s.stream); count_launches(s, 1); }
+        else { launch_rowsum(s.H, s.rowsum_partials, s.sumH, d, s.stream); count_launches(s, 2); }
+        s.rowsum_blocks = 0;
+    });
     const float* P = s.packed; int nsplit = 1; size_t stride = 0;
     if (s.opt.engine == NMF_ENGINE_TCGEN05 && umma::fused_w_enabled(s)) {
         // both of the steps below in one kernel: the quotient goes from TMEM through shared memory into the
@@ -378,6 +384,7 @@ void session_run(nmf_session_impl& s, float thresh, int max_iter, double t[10], 
     const int every = s.opt.check_every;
     PhaseTimer* pt = t ? new PhaseTimer(s.stream) : nullptr;
     const bool graph = s.opt.use_graph && !pt;
+    s.rowsum_blocks = 0;
     if (graph) build_graphs(s);
 
     cudaEvent_t e0, e1;

@@ -28,6 +28,7 @@ struct nmf_session_impl {
     float *Hpart = nullptr; int hsplit = 1;       // split-M partial W'*Y of the H update (small problems only)
     int fhsplit = 1;                              // the same for the fused H step (shares Hpart)
     float *rowsum_partials = nullptr;
+    int rowsum_blocks = 0;                        // > 0: the H update of this iteration left that many partial row sums of the new H
     double *cost_partials = nullptr; int n_cost_partials = 0;
     int n_cost_partials_fused = 0;                // partials of the fused H step's cost variant (0: that step is not fused)
     float *Hbak = nullptr;                        // H before a fused H step that carries the cost (allocated on first use)
