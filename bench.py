@@ -2,7 +2,7 @@
 """bench.py — NMF iterations/s and effective TFLOP/s (8*M*N*K flop per iteration) of the update_div
 hot path on 1/2/4/8 B200 (BASELINE.json `metric`).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c4|c5|c2|c1|tiny]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c4|c3|c5|c5k64|c5k512|c5w|c5wk64|c5wk512|c2|c1|tiny]
 
 A "step" is one NMF iteration (H half-step + W half-step).  Workload at every N: BASELINE config C4
 "large synthetic NMF 16384x262144 K=256 column-sharded across 1/2/4/8 B200" — total work fixed, so
@@ -35,6 +35,10 @@ WORKLOADS = {                     # name: (M, N, K, seed, description)
     "c3s": (2049, 262144, 128, 3, "C3-shape 2049x262144 K=128"),
     "c5k64": (8192, 131072, 64, 5, "C5 8192x131072 K=64"),
     "c5k512": (8192, 131072, 512, 5, "C5 8192x131072 K=512"),
+    # BASELINE config 5 as a WEAK-scaling sweep: 131072 columns PER GPU (N = 131072 * g), seed 5 + log2(g)
+    "c5w": (8192, 131072, 256, 5, "C5 weak 8192x(131072*g) K=256"),
+    "c5wk64": (8192, 131072, 64, 5, "C5 weak 8192x(131072*g) K=64"),
+    "c5wk512": (8192, 131072, 512, 5, "C5 weak 8192x(131072*g) K=512"),
     "c2": (513, 20000, 40, 1, "C2 audio spectrogram 513x20000 K=40"),
     "c1": (4096, 350, 128, 0, "C1 bundled shape 4096x350 K=128"),
     "mid": (8192, 32768, 256, 7, "mid 8192x32768 K=256 (profiling size)"),
@@ -138,6 +142,10 @@ def main():
     M, N, K, seed, desc = WORKLOADS[args.workload]
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    weak = args.workload.startswith("c5w")
+    if weak:                                                  # per-GPU work fixed: the column count grows with the GPU count
+        N *= world; seed += max(0, world.bit_length() - 1)
+        desc = desc.replace("(131072*g)", str(N)) + f" (g={world})"
     if args.impl == "reference":
         return run_reference_arm(args, M, N, K, seed, desc, rank, world)
     args.warmup = max(args.warmup, 3)
@@ -278,7 +286,7 @@ def main():
     if rank == 0:
         line = {"metric": "nmf_iterations_per_s", "value": value, "unit": "iterations/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-                "scaling": "strong", "vs_baseline": None, "dtype": "f32 (3xTF32 tensor-core products, fp32 accumulate)",
+                "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f32 (3xTF32 tensor-core products, fp32 accumulate)",
                 "data": "synthetic",
                 "config": {"workload": desc, "M": M, "N": N, "K": K, "columns_per_gpu": n_loc,
                            "parallelism": f"column-sharded x{world}", "engine": args.engine,
