@@ -94,7 +94,8 @@ typedef struct {
     int check_every;    /* cost / convergence period; 0 => 25 (ITER_CHECK)                  */
     int use_graph;      /* 1: replay one CUDA graph per iteration (reference: nmf.cu:100-115) */
     int tf32_passes;    /* 3 = 3xTF32 (fp32-equivalent, default); 1 = single-pass TF32      */
-    int reserved[10];
+    int restarts;       /* sessions: R >= 1 factor pairs sharing X (batched restarts); 0 => 1 */
+    int reserved[9];
 } nmf_options;
 
 typedef struct {
@@ -114,6 +115,22 @@ const char *nmf_version(void);
 int nmf_update_div_ex(matrix W, matrix H, matrix X, float CONVERGE_THRESH, int max_iter,
                       double t[10], int verbose, const nmf_options *opt, nmf_result *res);
 
+/* Batched random restarts (the paper's reason for wanting speed: "several random initialisations" per
+ * decomposition, nmf_ismir_2009.pdf p.2 section 3.2; the reference runs exactly one, cuda/nmf.cu:42).
+ * W[r] (MxK), H[r] (KxN), r = 0..restarts-1: independent initial factor pairs for the SAME X, all updated in
+ * place exactly as `restarts` separate update_div calls would (each restart stops on its own convergence
+ * check), but in the same kernel launches: the restarts are stacked along k and every fused half-iteration
+ * kernel walks the work items of all of them, so small problems fill the GPU and X is shared.
+ *   iterations, converged, cost : per-restart arrays of length `restarts` (any may be NULL); cost = KL
+ *       divergence at the restart's last check (NaN if never evaluated: CONVERGE_THRESH = 0 and verbose = 0
+ *       evaluate it once at the end)
+ *   returns the index of the restart with the lowest cost ("keep the best"), or -1 on failure in error mode 1.
+ * Shapes the stacked kernels do not cover (K > 256, fewer than 129 rows or columns, refcompat semantics, single-pass
+ * TF32) run the restarts one after another through the same CUDA path. */
+int nmf_update_div_batch(matrix *W, matrix *H, int restarts, matrix X, float CONVERGE_THRESH, int max_iter,
+                         double t[10], int verbose, const nmf_options *opt,
+                         int *iterations, int *converged, double *cost);
+
 /* A session owns the device buffers of one rank's shard: W (M x K, replicated), the local column
  * block of H (K x n_local) and X (M x n_local).  n_offset / n_global locate the block in the
  * full problem (needed by the refcompat column mask and the synthetic generator). */
@@ -128,6 +145,22 @@ void nmf_session_destroy(nmf_session *s);
 int nmf_session_upload(nmf_session *s, const float *W, const float *H_local, const float *X_local);
 /* Device -> host; either may be NULL. */
 int nmf_session_download(nmf_session *s, float *W, float *H_local);
+/* Sessions created with opt->restarts = R > 1: the factors of restart r (same layouts as above; X is shared and
+ * goes up through nmf_session_upload(s, NULL, NULL, X)). */
+int nmf_session_upload_restart(nmf_session *s, int r, const float *W, const float *H_local);
+int nmf_session_download_restart(nmf_session *s, int r, float *W, float *H_local);
+/* Per-restart outcome of the last nmf_session_run: arrays of R entries, any may be NULL. */
+int nmf_session_restart_results(const nmf_session *s, int *iterations, int *converged, double *cost);
+/* One half of an iteration on the resident data: which = 0 the H step (cuda/nmf.cu:118-146), 1 the W step (:148-176).
+ * Parity tests use it to look at a full-size problem between the two halves. */
+int nmf_session_half_step(nmf_session *s, int which);
+/* `count` rows of the resident X (count x N, column-major, leading dimension count) and of W (count x K):
+ * the W step is row-local, so sampled rows of a full-size run can be checked against the oracle. */
+int nmf_session_download_rows(nmf_session *s, const int *rows, int count, float *Xr, float *Wr);
+/* `count` columns of the resident X (M x count) and H (K x count) by GLOBAL column index (inside this
+ * shard), unpadded, either output may be NULL: lets a full-size run be spot-checked against the oracle
+ * on sampled columns (the H step is column-local). */
+int nmf_session_download_cols(nmf_session *s, const long long *cols, int count, float *Xc, float *Hc);
 
 /* Synthetic uniform(0,1) data generated on the device from a counter-based hash of the GLOBAL
  * (row, col) index, so any column sharding yields the same problem.  which: bit0 W, bit1 H, bit2 X */
@@ -148,7 +181,8 @@ int nmf_session_share_comm(nmf_session *dst, nmf_session *src);
 int nmf_session_run(nmf_session *s, float CONVERGE_THRESH, int max_iter, double t[10], int verbose,
                     nmf_result *res);
 
-/* KL divergence of the resident factors (allreduced over ranks when joined). */
+/* KL divergence of the resident factors (allreduced over ranks when joined); R values for a session with
+ * R restarts. */
 int nmf_session_cost(nmf_session *s, double *cost);
 
 /* Which half-iterations this session runs as ONE kernel (the quotient never leaves the SM): bit 0 the W

@@ -42,7 +42,7 @@ class matrix(ctypes.Structure):
 class nmf_options(ctypes.Structure):
     _fields_ = [("semantics", ctypes.c_int), ("engine", ctypes.c_int), ("device", ctypes.c_int),
                 ("check_every", ctypes.c_int), ("use_graph", ctypes.c_int), ("tf32_passes", ctypes.c_int),
-                ("reserved", ctypes.c_int * 10)]
+                ("restarts", ctypes.c_int), ("reserved", ctypes.c_int * 9)]
 
 
 class nmf_result(ctypes.Structure):
@@ -69,11 +69,20 @@ _SIGNATURES = {
     "nmf_version": (ctypes.c_char_p, []),
     "nmf_update_div_ex": (ctypes.c_int, [matrix, matrix, matrix, ctypes.c_float, ctypes.c_int, _f64p, ctypes.c_int,
                                          ctypes.POINTER(nmf_options), ctypes.POINTER(nmf_result)]),
+    "nmf_update_div_batch": (ctypes.c_int, [ctypes.POINTER(matrix), ctypes.POINTER(matrix), ctypes.c_int, matrix, ctypes.c_float,
+                                            ctypes.c_int, _f64p, ctypes.c_int, ctypes.POINTER(nmf_options),
+                                            ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int), _f64p]),
     "nmf_session_create": (ctypes.c_void_p, [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_longlong,
                                              ctypes.c_longlong, ctypes.POINTER(nmf_options)]),
     "nmf_session_destroy": (None, [ctypes.c_void_p]),
     "nmf_session_upload": (ctypes.c_int, [ctypes.c_void_p, _f32p, _f32p, _f32p]),
     "nmf_session_download": (ctypes.c_int, [ctypes.c_void_p, _f32p, _f32p]),
+    "nmf_session_upload_restart": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _f32p, _f32p]),
+    "nmf_session_download_restart": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, _f32p, _f32p]),
+    "nmf_session_restart_results": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int), _f64p]),
+    "nmf_session_download_cols": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_longlong), ctypes.c_int, _f32p, _f32p]),
+    "nmf_session_download_rows": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.c_int, _f32p, _f32p]),
+    "nmf_session_half_step": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "nmf_session_fill_uniform": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_ulonglong, ctypes.c_int]),
     "nmf_nccl_unique_id": (ctypes.c_int, [ctypes.c_void_p]),
     "nmf_session_join": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
@@ -119,12 +128,13 @@ def _check(rc):
         raise NmfError(lib().nmf_last_error().decode(errors="replace"))
 
 
-def options(semantics="exact", engine="tcgen05", device=-1, check_every=25, use_graph=True, tf32_passes=3):
+def options(semantics="exact", engine="tcgen05", device=-1, check_every=25, use_graph=True, tf32_passes=3, restarts=1):
     o = nmf_options()
     lib().nmf_default_options(ctypes.byref(o))
     o.semantics = REFCOMPAT if semantics in ("refcompat", REFCOMPAT) else EXACT
     o.engine = ENGINE_SIMT if engine in ("simt", ENGINE_SIMT) else ENGINE_TCGEN05
     o.device, o.check_every, o.use_graph, o.tf32_passes = device, check_every, int(use_graph), tf32_passes
+    o.restarts = int(restarts)
     return o
 
 
@@ -176,12 +186,50 @@ def update_div(W, H, X, CONVERGE_THRESH=0.0, max_iter=200, t=None, verbose=0, op
     return res
 
 
+def update_div_plain(W, H, X, CONVERGE_THRESH=0.0, max_iter=200, t=None, verbose=0):
+    """The reference-facing symbol itself — `void update_div(matrix W, matrix H, matrix X, float, int, double t[10],
+    int verbose)`, structs by value, no options, no result record (README.md:38-54).  Semantics / engine come from the
+    environment (NMF_SEMANTICS, ...), as for a C caller.  W and H are updated in place."""
+    for a in (W, H):
+        if not (isinstance(a, np.ndarray) and a.dtype == np.float32 and a.flags.f_contiguous and a.flags.writeable):
+            raise TypeError("W and H must be writable float32 column-major (order='F') numpy arrays")
+    Xf = _f(X)
+    mw, mh, mx = matrix.from_numpy(W), matrix.from_numpy(H), matrix.from_numpy(Xf)
+    tp = t.ctypes.data_as(_f64p) if t is not None else None
+    L = lib()
+    L.update_div(mw, mh, mx, float(CONVERGE_THRESH), int(max_iter), tp, int(verbose))   # void: in error mode 1 it returns early
+    err = L.nmf_last_error()
+    if err:
+        raise NmfError(err.decode(errors="replace"))
+
+
+def update_div_batch(Ws, Hs, X, CONVERGE_THRESH=0.0, max_iter=200, t=None, verbose=0, opt=None):
+    """R restarts (lists of R float32 Fortran-ordered W (MxK) and H (KxN) arrays, updated in place) on the same X in the
+    same kernel launches; returns (best index, iterations[R], converged[R], cost[R])."""
+    R = len(Ws)
+    assert R == len(Hs) and R >= 1
+    for a in list(Ws) + list(Hs):
+        if not (isinstance(a, np.ndarray) and a.dtype == np.float32 and a.flags.f_contiguous and a.flags.writeable):
+            raise TypeError("W[r] and H[r] must be writable float32 column-major (order='F') numpy arrays")
+    Xf = _f(X)
+    mws = (matrix * R)(*[matrix.from_numpy(a) for a in Ws])
+    mhs = (matrix * R)(*[matrix.from_numpy(a) for a in Hs])
+    its = (ctypes.c_int * R)(); conv = (ctypes.c_int * R)(); cost = (ctypes.c_double * R)()
+    tp = t.ctypes.data_as(_f64p) if t is not None else None
+    best = lib().nmf_update_div_batch(mws, mhs, R, matrix.from_numpy(Xf), float(CONVERGE_THRESH), int(max_iter), tp,
+                                      int(verbose), ctypes.byref(opt) if opt is not None else None, its, conv, cost)
+    if best < 0:
+        raise NmfError(lib().nmf_last_error().decode(errors="replace"))
+    return best, list(its), list(conv), list(cost)
+
+
 # ------------------------------------------------------------------------------------------
 # sessions: device-resident shard of one rank
 # ------------------------------------------------------------------------------------------
 class Session:
     def __init__(self, M, n_local, K, n_offset=0, n_global=None, opt=None):
         self.M, self.N, self.K = int(M), int(n_local), int(K)
+        self.R = max(1, int(opt.restarts)) if opt is not None else 1
         self._opt = opt
         h = lib().nmf_session_create(self.M, self.N, self.K, int(n_offset),
                                      int(n_global if n_global is not None else n_local),
@@ -213,6 +261,41 @@ class Session:
         _check(lib().nmf_session_download(self._h, _p(W), _p(H)))
         return W, H
 
+    def upload_restart(self, r, W=None, H=None):
+        W = None if W is None else _f(W); H = None if H is None else _f(H)
+        _check(lib().nmf_session_upload_restart(self._h, int(r), _p(W), _p(H)))
+
+    def download_restart(self, r):
+        W = np.empty((self.M, self.K), dtype=np.float32, order="F")
+        H = np.empty((self.K, self.N), dtype=np.float32, order="F")
+        _check(lib().nmf_session_download_restart(self._h, int(r), _p(W), _p(H)))
+        return W, H
+
+    def restart_results(self):
+        its = (ctypes.c_int * self.R)(); conv = (ctypes.c_int * self.R)(); cost = (ctypes.c_double * self.R)()
+        _check(lib().nmf_session_restart_results(self._h, its, conv, cost))
+        return list(its), list(conv), list(cost)
+
+    def download_cols(self, cols):
+        """columns `cols` (global indices inside this shard) of the resident X (M x len) and H (K x len)"""
+        c = np.ascontiguousarray(cols, dtype=np.int64)
+        Xc = np.empty((self.M, c.size), dtype=np.float32, order="F")
+        Hc = np.empty((self.K, c.size), dtype=np.float32, order="F")
+        _check(lib().nmf_session_download_cols(self._h, c.ctypes.data_as(ctypes.POINTER(ctypes.c_longlong)), int(c.size), _p(Xc), _p(Hc)))
+        return Xc, Hc
+
+    def download_rows(self, rows):
+        """rows `rows` of the resident X (len x N) and W (len x K)"""
+        r = np.ascontiguousarray(rows, dtype=np.int32)
+        Xr = np.empty((r.size, self.N), dtype=np.float32, order="F")
+        Wr = np.empty((r.size, self.K), dtype=np.float32, order="F")
+        _check(lib().nmf_session_download_rows(self._h, r.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), int(r.size), _p(Xr), _p(Wr)))
+        return Xr, Wr
+
+    def half_step(self, which):
+        """which = "h" | "w": one half of an iteration on the resident data"""
+        _check(lib().nmf_session_half_step(self._h, 0 if which in (0, "h", "H") else 1))
+
     def fill_uniform(self, seed, which=7):
         _check(lib().nmf_session_fill_uniform(self._h, int(seed), int(which)))
 
@@ -239,9 +322,10 @@ class Session:
         return res
 
     def cost(self):
-        c = ctypes.c_double()
-        _check(lib().nmf_session_cost(self._h, ctypes.byref(c)))
-        return c.value
+        """KL divergence of the resident factors (a list of R values for a session with R > 1 restarts)"""
+        c = (ctypes.c_double * self.R)()
+        _check(lib().nmf_session_cost(self._h, c))
+        return c[0] if self.R == 1 else list(c)
 
 
 def nccl_unique_id():

@@ -19,6 +19,11 @@ void session_fill_uniform(nmf_session_impl& s, unsigned long long seed, int whic
 void session_fill_planted(nmf_session_impl& s, unsigned long long seed, int rank, float noise);
 void session_run(nmf_session_impl& s, float thresh, int max_iter, double t[10], int verbose, nmf_result* res);
 void session_cost(nmf_session_impl& s, double* cost);
+void session_upload_restart(nmf_session_impl& s, int r, const float* W, const float* H);
+void session_download_restart(nmf_session_impl& s, int r, float* W, float* H);
+void session_download_cols(nmf_session_impl& s, const long long* cols, int count, float* Xc, float* Hc);
+void session_download_rows(nmf_session_impl& s, const int* rows, int count, float* Xr, float* Wr);
+void session_half_step(nmf_session_impl& s, int which);
 }  // namespace nmf
 
 using namespace nmf;
@@ -32,6 +37,7 @@ thread_local std::string g_last_error;
 // exit(code)) or, in mode 1, records the message and returns the code.
 int guarded(const std::function<void()>& body) {
     try {
+        g_last_error.clear();          // nmf_last_error() is empty after a call that succeeded
         body();
         return 0;
     } catch (const Error& e) {
@@ -158,43 +164,62 @@ void column_shard(long long N, int rank, int world, long long* first, long long*
 
 // update_div on g GPUs of this box from ONE process: a host thread per GPU, X and H sharded by columns,
 // W replicated, one NCCL allreduce per iteration — what `NMF_NUM_GPUS=g ./nmf` runs.
+// Every rank gets the same thresh / max_iter / verbose (the collective schedule depends on them; only rank 0 prints).
+// Failure handling: the shards are validated here, before any thread exists; sessions are created and filled in a first
+// phase that contains no collective; the communicators are made in one ncclCommInitAll call on this thread; and a rank
+// that fails inside the iteration aborts every communicator so that its peers return instead of waiting for it.
 void update_div_multi(matrix W, matrix H, matrix X, float thresh, int max_iter, double t[10], int verbose,
                       const nmf_options& o, int g, nmf_result* res) {
     const int M = W.dim[0], K = W.dim[1];
     const long long N = H.dim[1];
-    unsigned char uid[128];
-    nccl_unique_id(uid);
     const int dev0 = o.device >= 0 ? o.device : 0;
-    std::vector<std::thread> threads;
+    std::vector<long long> first((size_t)g), count((size_t)g);
+    for (int r = 0; r < g; ++r) {
+        column_shard(N, r, g, &first[(size_t)r], &count[(size_t)r]);
+        NMF_CHECK(count[(size_t)r] > 0, "update_div: internal error: empty column shard");
+    }
+    std::vector<std::unique_ptr<nmf_session_impl>> sess((size_t)g);
     std::vector<std::string> errors((size_t)g);
     std::vector<nmf_result> results((size_t)g);
-    for (int r = 0; r < g; ++r) {
-        threads.emplace_back([&, r] {
-            try {
-                long long first = 0, count = 0;
-                column_shard(N, r, g, &first, &count);
-                NMF_CHECK(count > 0, "update_div: fewer 256-column blocks than GPUs (lower NMF_NUM_GPUS)");
-                nmf_options orank = o;
-                orank.device = dev0 + r;
-                std::unique_ptr<nmf_session_impl> s(session_create(M, (int)count, K, first, N, orank));
-                nccl_join(*s, r, g, uid);
-                session_upload(*s, W.mat, H.mat + (size_t)first * K, X.mat + (size_t)first * M);
-                session_run(*s, thresh, max_iter, r == 0 ? t : nullptr, r == 0 ? verbose : 0, &results[(size_t)r]);
-                session_download(*s, r == 0 ? W.mat : nullptr, H.mat + (size_t)first * K);
-            } catch (const std::exception& e) {
-                errors[(size_t)r] = e.what();
-                if (errors[(size_t)r].empty()) errors[(size_t)r] = "unknown error";
-            }
-        });
+    auto run_phase = [&](const std::function<void(int)>& body, bool abort_peers) {
+        std::vector<std::thread> threads;
+        for (int r = 0; r < g; ++r) {
+            threads.emplace_back([&, r] {
+                try { body(r); }
+                catch (const std::exception& e) {
+                    errors[(size_t)r] = e.what();
+                    if (errors[(size_t)r].empty()) errors[(size_t)r] = "unknown error";
+                    if (abort_peers) for (int q = 0; q < g; ++q) if (sess[(size_t)q]) nccl_abort(*sess[(size_t)q]);
+                }
+            });
+        }
+        for (auto& th : threads) th.join();
+        for (int r = 0; r < g; ++r) NMF_CHECK(errors[(size_t)r].empty(), "GPU " + std::to_string(dev0 + r) + ": " + errors[(size_t)r]);
+    };
+    run_phase([&](int r) {
+        nmf_options orank = o;
+        orank.device = dev0 + r;
+        sess[(size_t)r].reset(session_create(M, (int)count[(size_t)r], K, first[(size_t)r], N, orank));
+        session_upload(*sess[(size_t)r], W.mat, H.mat + (size_t)first[(size_t)r] * K, X.mat + (size_t)first[(size_t)r] * M);
+    }, false);
+    {
+        std::vector<nmf_session_impl*> raw;
+        for (auto& p : sess) raw.push_back(p.get());
+        nccl_init_all(raw.data(), g);
     }
-    for (auto& th : threads) th.join();
-    for (int r = 0; r < g; ++r) NMF_CHECK(errors[(size_t)r].empty(), "GPU " + std::to_string(dev0 + r) + ": " + errors[(size_t)r]);
+    run_phase([&](int r) {
+        session_run(*sess[(size_t)r], thresh, max_iter, r == 0 ? t : nullptr, verbose, &results[(size_t)r]);
+        session_download(*sess[(size_t)r], r == 0 ? W.mat : nullptr, H.mat + (size_t)first[(size_t)r] * K);
+    }, true);
     if (res) *res = results[0];
 }
 
-int env_num_gpus() {
+// NMF_NUM_GPUS, limited to the 256-column blocks there are to hand out (a GPU without columns has nothing to do)
+int resolve_num_gpus(long long N) {
     const char* v = std::getenv("NMF_NUM_GPUS");
-    return (v && *v) ? std::max(1, std::atoi(v)) : 1;
+    const int want = (v && *v) ? std::max(1, std::atoi(v)) : 1;
+    const long long nblocks = (N + 255) / 256;
+    return (int)std::min<long long>(want, std::max<long long>(1, nblocks));
 }
 
 }  // namespace
@@ -208,7 +233,7 @@ int nmf_update_div_ex(matrix W, matrix H, matrix X, float CONVERGE_THRESH, int m
         NMF_CHECK(max_iter >= 0, "update_div: max_iter must be >= 0");
         const nmf_options o = resolve(opt);
         // the GPU count is not in the reference's signature (README.md:39-47): NMF_NUM_GPUS selects it
-        int g = env_num_gpus();
+        const int g = resolve_num_gpus(H.dim[1]);
         if (g > 1) {
             int ndev = 0;
             CUDA_CHECK(cudaGetDeviceCount(&ndev));
@@ -217,20 +242,87 @@ int nmf_update_div_ex(matrix W, matrix H, matrix X, float CONVERGE_THRESH, int m
             if (t) t[PH_TOTAL] = std::chrono::duration<double>(clk::now() - w0).count();
             return;
         }
-        nmf_session_impl* s = session_create(W.dim[0], H.dim[1], W.dim[1], 0, H.dim[1], o);
-        try {
-            session_upload(*s, W.mat, H.mat, X.mat);
-            const double setup = std::chrono::duration<double>(clk::now() - w0).count();
-            session_run(*s, CONVERGE_THRESH, max_iter, t, verbose, res);
-            const auto d0 = clk::now();
-            session_download(*s, W.mat, H.mat);
-            if (t) {
-                t[PH_SETUP] = setup + std::chrono::duration<double>(clk::now() - d0).count();
-                t[PH_TOTAL] = std::chrono::duration<double>(clk::now() - w0).count();
-            }
-        } catch (...) { delete s; throw; }
-        delete s;
+        nmf_options o1 = o; o1.restarts = 1;
+        std::unique_ptr<nmf_session_impl> s(session_create(W.dim[0], H.dim[1], W.dim[1], 0, H.dim[1], o1));
+        session_upload(*s, W.mat, H.mat, X.mat);
+        const double setup = std::chrono::duration<double>(clk::now() - w0).count();
+        session_run(*s, CONVERGE_THRESH, max_iter, t, verbose, res);
+        const auto d0 = clk::now();
+        session_download(*s, W.mat, H.mat);
+        if (t) {
+            t[PH_SETUP] = setup + std::chrono::duration<double>(clk::now() - d0).count();
+            t[PH_TOTAL] = std::chrono::duration<double>(clk::now() - w0).count();
+        }
     });
+}
+
+int nmf_update_div_batch(matrix* W, matrix* H, int restarts, matrix X, float CONVERGE_THRESH, int max_iter,
+                         double t[10], int verbose, const nmf_options* opt, int* iterations, int* converged, double* cost) {
+    int best = -1;
+    const int rc = guarded([&] {
+        using clk = std::chrono::steady_clock;
+        const auto w0 = clk::now();
+        NMF_CHECK(W && H && restarts >= 1 && restarts <= 64, "update_div_batch: need 1..64 restarts");
+        for (int r = 0; r < restarts; ++r) {
+            check_shapes(W[r], H[r], X);
+            NMF_CHECK(W[r].dim[1] == W[0].dim[1], "update_div_batch: every restart must have the same K");
+        }
+        NMF_CHECK(max_iter >= 0, "update_div: max_iter must be >= 0");
+        nmf_options o = resolve(opt);
+        const int M = X.dim[0], N = X.dim[1], K = W[0].dim[1];
+        std::vector<int> its((size_t)restarts, 0), conv((size_t)restarts, 0);
+        std::vector<double> costs((size_t)restarts, std::nan(""));
+        if (t) for (int i = 0; i < 10; ++i) t[i] = 0.0;
+        // the stacked path needs both half-iterations fused; anything else runs the restarts one after another
+        bool stacked = restarts > 1 && o.engine == NMF_ENGINE_TCGEN05 && o.semantics == NMF_EXACT && o.tf32_passes == 3;
+        if (stacked) {
+            int ndev = 0; CUDA_CHECK(cudaGetDeviceCount(&ndev));
+            NMF_CHECK(ndev > 0, "no CUDA device: libnmf_b200 has no CPU fallback");
+            if (o.device >= 0) CUDA_CHECK(cudaSetDevice(o.device));
+            const umma::Tuning tn = umma::read_tuning();
+            const Dims d = make_dims(M, N, K, 0, N, o.semantics, restarts, tn.pad64 != 0);
+            stacked = umma::fused_both_wanted(d, o.tf32_passes, tn);
+        }
+        if (stacked) {
+            o.restarts = restarts;
+            std::unique_ptr<nmf_session_impl> s(session_create(M, N, K, 0, N, o));
+            session_upload(*s, nullptr, nullptr, X.mat);
+            for (int r = 0; r < restarts; ++r) session_upload_restart(*s, r, W[r].mat, H[r].mat);
+            const double setup = std::chrono::duration<double>(clk::now() - w0).count();
+            nmf_result res{};
+            session_run(*s, CONVERGE_THRESH, max_iter, t, verbose, &res);
+            if (std::isnan(s->costs[0])) session_cost(*s, s->costs.data());     // keep-best needs the costs even when no check ran
+            const auto d0 = clk::now();
+            for (int r = 0; r < restarts; ++r) {
+                session_download_restart(*s, r, W[r].mat, H[r].mat);
+                its[(size_t)r] = s->iters_r[(size_t)r]; conv[(size_t)r] = s->conv_r[(size_t)r]; costs[(size_t)r] = s->costs[(size_t)r];
+            }
+            if (t) t[PH_SETUP] = setup + std::chrono::duration<double>(clk::now() - d0).count();
+        } else {
+            o.restarts = 1;
+            std::unique_ptr<nmf_session_impl> s(session_create(M, N, K, 0, N, o));
+            session_upload(*s, nullptr, nullptr, X.mat);                         // X goes up once
+            for (int r = 0; r < restarts; ++r) {
+                double tr[10];
+                session_upload(*s, W[r].mat, H[r].mat, nullptr);
+                nmf_result res{};
+                session_run(*s, CONVERGE_THRESH, max_iter, t ? tr : nullptr, verbose, &res);
+                if (std::isnan(res.cost)) session_cost(*s, &res.cost);
+                session_download(*s, W[r].mat, H[r].mat);
+                its[(size_t)r] = res.iterations; conv[(size_t)r] = res.converged; costs[(size_t)r] = res.cost;
+                if (t) for (int i = 0; i < 8; ++i) t[i] += tr[i];
+            }
+        }
+        if (t) t[PH_TOTAL] = std::chrono::duration<double>(clk::now() - w0).count();
+        best = 0;
+        for (int r = 1; r < restarts; ++r) if (costs[(size_t)r] < costs[(size_t)best]) best = r;
+        for (int r = 0; r < restarts; ++r) {
+            if (iterations) iterations[r] = its[(size_t)r];
+            if (converged) converged[r] = conv[(size_t)r];
+            if (cost) cost[r] = costs[(size_t)r];
+        }
+    });
+    return rc == 0 ? best : -1;
 }
 
 void update_div(matrix W, matrix H, matrix X, float CONVERGE_THRESH, int max_iter, double t[10], int verbose) {
@@ -254,6 +346,31 @@ int nmf_session_upload(nmf_session* s, const float* W, const float* H, const flo
 }
 int nmf_session_download(nmf_session* s, float* W, float* H) {
     return guarded([&] { NMF_CHECK(s, "NULL session"); session_download(*s, W, H); });
+}
+int nmf_session_upload_restart(nmf_session* s, int r, const float* W, const float* H) {
+    return guarded([&] { NMF_CHECK(s, "NULL session"); session_upload_restart(*s, r, W, H); });
+}
+int nmf_session_download_restart(nmf_session* s, int r, float* W, float* H) {
+    return guarded([&] { NMF_CHECK(s, "NULL session"); session_download_restart(*s, r, W, H); });
+}
+int nmf_session_restart_results(const nmf_session* s, int* iterations, int* converged, double* cost) {
+    return guarded([&] {
+        NMF_CHECK(s, "NULL session");
+        for (int r = 0; r < s->d.R; ++r) {
+            if (iterations) iterations[r] = s->iters_r[(size_t)r];
+            if (converged) converged[r] = s->conv_r[(size_t)r];
+            if (cost) cost[r] = s->costs[(size_t)r];
+        }
+    });
+}
+int nmf_session_download_rows(nmf_session* s, const int* rows, int count, float* Xr, float* Wr) {
+    return guarded([&] { NMF_CHECK(s && rows, "bad arguments"); session_download_rows(*s, rows, count, Xr, Wr); });
+}
+int nmf_session_half_step(nmf_session* s, int which) {
+    return guarded([&] { NMF_CHECK(s && (which == 0 || which == 1), "bad arguments"); session_half_step(*s, which); });
+}
+int nmf_session_download_cols(nmf_session* s, const long long* cols, int count, float* Xc, float* Hc) {
+    return guarded([&] { NMF_CHECK(s && cols && count >= 0, "bad arguments"); session_download_cols(*s, cols, count, Xc, Hc); });
 }
 int nmf_session_fill_uniform(nmf_session* s, unsigned long long seed, int which) {
     return guarded([&] { NMF_CHECK(s, "NULL session"); session_fill_uniform(*s, seed, which); });
@@ -289,10 +406,11 @@ static void with_session(const float* W, const float* H, const float* X, int M, 
                          const std::function<void(nmf_session_impl&)>& body) {
     nmf_options o = resolve(opt);
     o.use_graph = 0;
-    nmf_session_impl* s = session_create(M, N, K, 0, N, o);
-    try { session_upload(*s, W, H, X); body(*s); CUDA_CHECK(cudaStreamSynchronize(s->stream)); }
-    catch (...) { delete s; throw; }
-    delete s;
+    o.restarts = 1;
+    std::unique_ptr<nmf_session_impl> s(session_create(M, N, K, 0, N, o));
+    session_upload(*s, W, H, X);
+    body(*s);
+    CUDA_CHECK(cudaStreamSynchronize(s->stream));
 }
 
 int nmf_dbg_quotient(const float* W, const float* H, const float* X, float* Y, double* cost,

@@ -47,9 +47,13 @@ inline int ref_pad32(int v) { return (v != 1 && v % 32 != 0) ? v + (32 - v % 32)
 //       refcompat : the reference's padded dims (cuda/matrix.cu:88-95) with EPS fill, because its
 //                   clamp runs over the whole padded buffer (cuda/nmf.cu:211).
 //   leading dimensions: ldM = Mv (W, X, Y, P), ldK = Kv (H) — multiples of 32 floats (128 B).
+//   restarts  : R >= 1 factor pairs that share X (batched random initialisations), stacked along k: W is
+//               [Mv x R*Kr], H is [R*Kr x Nv]; Kr = the padded K of ONE restart and Kv = R*Kr is what every
+//               elementwise / per-k kernel iterates over (restart r owns k in [r*Kr, r*Kr + K)).
 struct Dims {
     int M = 0, N = 0, K = 0;
     int Mv = 0, Nv = 0, Kv = 0;
+    int R = 1, Kr = 0;       // restarts and the padded K of one of them (Kv = R * Kr)
     int Nva = 0;             // columns ALLOCATED for X, Y, H (Nv rounded up to 768 = lcm of the GEMM tile widths, zero fill):
                              // lets the fused epilogues store whole tiles without per-element column predicates
     long long n_offset = 0, n_global = 0;
@@ -62,7 +66,8 @@ struct Dims {
     size_t szXa() const { return (size_t)Mv * Nva; }
 };
 
-Dims make_dims(int M, int n_local, int K, long long n_offset, long long n_global, int semantics);
+Dims make_dims(int M, int n_local, int K, long long n_offset, long long n_global, int semantics,
+               int restarts = 1, bool pad_k64 = false);
 
 // ---------------------------------------------------------------------------------------------
 // Small kernels (kernels_small.cu).  All take the stream explicitly; none synchronises.
@@ -94,6 +99,10 @@ void launch_rowsum(const float* H, float* partials, float* sumH, const Dims& d, 
 void launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nsplit, size_t split_stride,
                      const float* sumH, const Dims& d, cudaStream_t st);
 
+// dst[j*count + i] = src[j*ld + rows[i]] for j < cols (rows = device array of `count` row indices): sampled rows of a
+// column-major matrix, for the spot checks of full-size runs
+void launch_gather_rows(const float* src, int ld, int cols, const int* rows, int count, float* dst, cudaStream_t st);
+
 // out[e] = sum_s P[s][e] in split order (multi-GPU: fold the local splits before the allreduce).
 void launch_fold_splits(const float* P, int nsplit, size_t split_stride, float* out, size_t n, cudaStream_t st);
 // H <- H .* ((sum of the nsplit partial W'*Y) ./ max(sumW,EPS)), plus the TF32 pair of the new H
@@ -104,8 +113,8 @@ int  launch_update_h(float* H, float* Hhi, float* Hlo, const float* P, int nspli
 // sumH = ordered fold of the `nblocks` partial row sums launch_update_h left in `partials`
 void launch_rowsum_finish2(const float* partials, float* sumH, int nblocks, const Dims& d, cudaStream_t st);
 
-// cost = sum of `n` double partials (ordered).
-void launch_sum_partials(const double* partials, int n, double* out, cudaStream_t st);
+// out[b] = sum of the `n` double partials of batch b (partials + b*n), fixed order; nbatch blocks.
+void launch_sum_partials(const double* partials, int n, int nbatch, double* out, cudaStream_t st);
 
 // ---------------------------------------------------------------------------------------------
 // SIMT engine (kernels_simt.cu): fp32 FFMA GEMMs with the same fused epilogues.  Bring-up aid.

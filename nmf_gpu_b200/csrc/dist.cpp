@@ -3,7 +3,9 @@
 // NCCL is dlopen'ed so that the single-GPU path has no dependency on it; inside a torch process
 // the soname resolves to the libnccl torch already loaded.
 #include <dlfcn.h>
+#include <atomic>
 #include <cstring>
+#include <vector>
 
 #include "session.hpp"
 
@@ -20,6 +22,8 @@ struct Api {
     int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*CommAbort)(ncclComm_t) = nullptr;
+    int (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
 };
 
@@ -34,6 +38,8 @@ Api& api() {
     a.CommInitRank   = (int (*)(ncclComm_t*, int, ncclUniqueId, int))sym("ncclCommInitRank");
     a.AllReduce      = (int (*)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t))sym("ncclAllReduce");
     a.CommDestroy    = (int (*)(ncclComm_t))sym("ncclCommDestroy");
+    a.CommAbort      = (int (*)(ncclComm_t))sym("ncclCommAbort");
+    a.CommInitAll    = (int (*)(ncclComm_t*, int, const int*))sym("ncclCommInitAll");
     a.GetErrorString = (const char* (*)(int))sym("ncclGetErrorString");
     return a;
 }
@@ -43,7 +49,7 @@ void check(int r, const char* what) {
 }
 }  // namespace
 
-struct Nccl { ncclComm_t comm = nullptr; int refs = 1; };   // shared by the sessions of one process (nccl_share)
+struct Nccl { ncclComm_t comm = nullptr; int refs = 1; std::atomic<bool> aborted{false}; };   // shared by the sessions of one process (nccl_share)
 
 int nccl_unique_id(void* id128) {
     ncclUniqueId id;
@@ -63,6 +69,33 @@ void nccl_join(nmf_session_impl& s, int rank, int nranks, const void* id128) {
     const int r = api().CommInitRank(&n->comm, nranks, id, rank);
     if (r != 0) { delete n; check(r, "ncclCommInitRank"); }
     s.nccl = n; s.rank = rank; s.nranks = nranks;
+}
+
+// One process, a host thread per GPU (update_div with NMF_NUM_GPUS = g): all g communicators in ONE call from the
+// calling thread — no rank can be left waiting in ncclCommInitRank for a peer that failed before it got there.
+void nccl_init_all(nmf_session_impl* const* sessions, int g) {
+    if (g <= 1) { if (g == 1) { sessions[0]->rank = 0; sessions[0]->nranks = 1; } return; }
+    std::vector<int> devs((size_t)g);
+    std::vector<ncclComm_t> comms((size_t)g, nullptr);
+    for (int r = 0; r < g; ++r) {
+        NMF_CHECK(sessions[r]->g_full == nullptr && sessions[r]->nccl == nullptr, "join the communicator before the first run, once");
+        devs[(size_t)r] = sessions[r]->device;
+    }
+    check(api().CommInitAll(comms.data(), g, devs.data()), "ncclCommInitAll");
+    for (int r = 0; r < g; ++r) {
+        auto* n = new Nccl();
+        n->comm = comms[(size_t)r];
+        sessions[r]->nccl = n; sessions[r]->rank = r; sessions[r]->nranks = g;
+    }
+}
+
+// A rank that failed inside the iteration calls this on EVERY session of the process: peers blocked in a collective
+// that will never complete return with an error instead of hanging the call.
+void nccl_abort(nmf_session_impl& s) {
+    Nccl* n = s.nccl;
+    if (!n || !n->comm) return;
+    if (n->aborted.exchange(true)) return;
+    api().CommAbort(n->comm);
 }
 
 void nccl_allreduce_f32(nmf_session_impl& s, float* buf, size_t n) {
@@ -88,7 +121,7 @@ void nccl_share(nmf_session_impl& dst, nmf_session_impl& src) {
 void nccl_destroy(Nccl* n) {
     if (!n) return;
     if (--n->refs > 0) return;
-    if (n->comm) api().CommDestroy(n->comm);
+    if (n->comm && !n->aborted.load()) api().CommDestroy(n->comm);     // ncclCommAbort already freed an aborted communicator
     delete n;
 }
 

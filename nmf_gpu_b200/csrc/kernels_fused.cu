@@ -1,4 +1,4 @@
-// umma_fused.inc — the fused half-iteration kernels of the tcgen05 engine (included by kernels_umma.cu).
+// kernels_fused.cu — the fused half-iteration kernels of the tcgen05 engine.
 //
 //   W step (HSTEP = false)   P[m,k] = sum_n ( X[m,n] / max( (W*H)[m,n], EPS ) ) * H[k,n]         nmf.cu:155-168
 //   H step (HSTEP = true )   H[k,n] *= ( sum_m W[m,k] * X[m,n] / max( (W*H)[m,n], EPS ) ) / sumW[k]   nmf.cu:125-145
@@ -35,53 +35,11 @@
 // a-stages of tile g+1 BEFORE the b-stages of tile g, so S of the next tile is complete while the workers are still
 // dividing the current one: they never wait for the S GEMM (with one S tile that wait was 26 % of their time at
 // K = 128, ncu source page of C3) and the drain of a tile's P is taken after the first quotient chunk of the next tile.
+#include <atomic>
+
+#include "umma_fused.cuh"
+
 namespace nmf { namespace umma {
-
-constexpr int F_STAGES = 3;
-constexpr int F_STAGE_BYTES = 64 * 1024;           // A hi, A lo (16 KB each) + B hi, B lo (16 KB each)
-constexpr int F_B_TILE = 16 * 1024;
-constexpr int F_BN = 256;                          // S tile width (one S tile + P fill the 512 TMEM columns when K = 256)
-constexpr int F_BN_DB = 128;                       // K <= 128: two 128-wide S tiles (double-buffered) + P of <= 128 columns
-constexpr int F_NCH = F_BN / 32;                   // 32-column chunks per tile (upper bound)
-// NW = worker warps per TMEM lane quadrant (each takes 32 / NW columns of every S chunk and every NW-th chunk of P):
-//   NW = 2 : 384 threads, setmaxnreg 48 / 224 (launch gives 168: 120 x 128 released >= 56 x 256 acquired); P up to 256 columns
-//   NW = 4 : 640 threads, setmaxnreg 40 / 104 (launch gives 96: 56 x 128 released >= 8 x 512 acquired); P up to 128 columns —
-//            with K <= 128 the MMAs of a chunk take half as long and the quotient is the bound, so twice the warps work on it
-template <int NW> struct FCfg {
-    static constexpr int NTHREADS = 128 + 128 * NW;
-    static constexpr int REGS_CTRL = NW == 2 ? 48 : 40, REGS_WORK = NW == 2 ? 224 : 104;
-    static constexpr int CW = 32 / NW;                 // S / X / Y columns per thread and chunk
-    static constexpr int ACC = NW == 2 ? 4 : 1;        // 32-column chunks of P a thread accumulates (chunks h, h + NW, ..)
-    static constexpr int NARR = 4 * NW;                // worker warps per CTA (arrival counts)
-};
-constexpr int F_WORK_WARP0 = 4;
-constexpr int F_YRING = 4;                         // yfull barriers (> ring depth, see the workers)
-constexpr int F_XBUF_BYTES = BM * 32 * 4;          // one X chunk of this CTA: 128 lane rows x 32 columns fp32
-constexpr int F_XBUFS = 2;
-constexpr int F_EMPTY_WAYS = 4;                    // `empty` barriers per ring slot, taken in turn by the slot's uses (see the kernel)
-constexpr int F_SMEM_BYTES = F_STAGES * F_STAGE_BYTES + F_XBUFS * F_XBUF_BYTES + 1024 /*align*/ + 512 /*barriers*/;
-
-struct alignas(64) FusedParams {
-    CUtensorMap mapWhi, mapWlo;      // W pair [Mv x Kv], MN-major boxes 32 x 32      (a-stages: A in the W step, B in the H step)
-    CUtensorMap mapHhi, mapHlo;      // H pair [Kv x Nv], K-major boxes 32 x 128      (a-stages: B in the W step, A in the H step)
-    CUtensorMap mapGhi, mapGlo;      // b-stage B: W step H pair, MN-major boxes 32 x 32; H step W pair, K-major boxes 32 x Kv/2
-    CUtensorMap mapX;                // X [Mv x Nv]: W step boxes 128 m x 32 n (no swizzle), H step boxes 32 m x 128 n (128B swizzle)
-    int Ldim, Cdim, Kv;              // extents of the lane-row and tile-column dimensions (W step Mv, Nv; H step Nv, Mv)
-    int tiles_l, nsplit, ntiles_c;   // 256-row blocks of L, splits of the C range, 256-wide tiles of C
-    int kblocks;                     // Kv / 32
-    int period;                      // chunks accumulated in TMEM between promotions of P
-    int hintW, hintH, hintS;
-    // W step output: partial numerators P[split][m + k*ldP]; H step with nsplit > 1: partial W'*Y sums P[split][k + n*Kv]
-    float* P; unsigned long long split_stride; int ldP;
-    // H step with nsplit == 1: the update itself
-    float* H; float* Hhi; float* Hlo; const float* sumW;
-    // COST instantiation (H step of a check iteration): the KL divergence of the factors the step starts from
-    // (reduce1d_div, cuda/matrix.cu:578-640) over the logical Llog x Clog block; one partial per worker warp and work item
-    double* cost_partials; int Llog, Clog;
-    int bn;                          // S tile width the launch runs with (256, or 128 double-buffered)
-    int defer;                       // H step: store W'*Y sums to P even when nsplit == 1, k_update_h applies the update
-    unsigned int* err;
-};
 
 // 16 consecutive fp32 columns of this warp's 32 TMEM lanes
 __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16]) {
@@ -145,7 +103,8 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
     const int lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     const int worker = (int)(blockIdx.x >> 1), nworkers = (int)(gridDim.x >> 1);
-    const int items = p.tiles_l * p.nsplit;
+    const int per_batch = p.tiles_l * p.nsplit;                    // work items of one restart
+    const int items = per_batch * p.nbatch;
     const int KB = p.kblocks;
     const int bnh2 = p.Kv >> 1;                                   // P columns this CTA stages per b-stage
 
@@ -185,7 +144,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
 
     // tile range (along C) of work item t = (lane-row block, split sp)
     auto tile_range = [&](int t, int& a, int& b) {
-        const int sp = t / p.tiles_l;
+        const int sp = (t / p.tiles_l) % p.nsplit;
         a = (int)((long long)sp * p.ntiles_c / p.nsplit); b = (int)((long long)(sp + 1) * p.ntiles_c / p.nsplit);
     };
     auto chunks_of = [&](int tj) { const int left = p.Cdim - tj * BN; return left >= BN ? NCH : (left + 31) >> 5; };
@@ -211,6 +170,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
         auto load_a = [&](const Cur& c) {                           // the KB a-stages of a tile: W and H pairs of k block s
             const int l0 = (c.t % p.tiles_l) * 2 * BM + (int)rank * BM;      // this CTA's lane rows
             const int c0 = c.tj * BN;
+            const int koff = (c.t / per_batch) * p.Kv;                        // this restart's k range
             for (int s = 0; s < KB; ++s) {
                 { uint32_t par; const uint32_t eb = empty_prev(stage, use, par); mbar_wait_a(eb, par, p.err, 11); }
                 if (elect_one()) {
@@ -218,7 +178,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                     const uint32_t sA = sb + stage * F_STAGE_BYTES;
                     const uint32_t sB = sA + 2 * A_TILE_BYTES;
                     if (rank == 0) mbar_arrive_expect_tx_a(full_a + stage * 8, bytes_a);
-                    const int r0 = s * BK;
+                    const int r0 = koff + s * BK;
                     const uint32_t sW = HSTEP ? sB : sA;
                     const uint32_t sH = HSTEP ? sA : sB;           // H: one K-major box (W step: BN/2 columns, H step: 128 lane rows)
                     const int w0 = HSTEP ? c0 + (int)rank * (BN / 2) : l0;
@@ -236,6 +196,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
         };
         auto load_b = [&](const Cur& c) {                           // the b-stages of a tile: G chunk (the Y chunk is written by the workers)
             const int c0 = c.tj * BN, nch = chunks_of(c.tj);
+            const int koff = (c.t / per_batch) * p.Kv + (int)rank * bnh2;    // this restart's k range, this CTA's half of it
             for (int s = 0; s < nch; ++s) {
                 { uint32_t par; const uint32_t eb = empty_prev(stage, use, par); mbar_wait_a(eb, par, p.err, 11); }
                 if (elect_one()) {
@@ -245,10 +206,10 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                     const int n0 = c0 + s * 32;
                     for (int h = 0; h < 2; ++h) {
                         const CUtensorMap* mG = h ? &p.mapGlo : &p.mapGhi;
-                        if (HSTEP) tma_load_2d_cg2_a(sB + h * F_B_TILE, mG, fullc, n0, (int)rank * bnh2, polW);
+                        if (HSTEP) tma_load_2d_cg2_a(sB + h * F_B_TILE, mG, fullc, n0, koff, polW);
                         else {
                             for (int j = 0; j < bnh2 / 32; ++j)
-                                tma_load_2d_cg2_a(sB + h * F_B_TILE + j * 4096, mG, fullc, (int)rank * bnh2 + 32 * j, n0, polH);
+                                tma_load_2d_cg2_a(sB + h * F_B_TILE + j * 4096, mG, fullc, koff + 32 * j, n0, polH);
                         }
                     }
                 }
@@ -423,6 +384,8 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
             const int l = (t % p.tiles_l) * 2 * BM + rowoff;             // this thread's lane row (W step: m, H step: n)
             const bool row_ok = l < p.Ldim;
             const bool row_log = l < p.Llog;             // COST: the lane row lies inside the logical matrix
+            const int koff = (t / per_batch) * p.Kv;     // this restart's k range
+            const int sp = (t / p.tiles_l) % p.nsplit;
             double cost_item = 0.0;
             int nt0, nt1; tile_range(t, nt0, nt1);
             #pragma unroll
@@ -533,7 +496,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
             if (row_ok) {
                 if (HSTEP && (p.nsplit > 1 || p.defer)) {
                     // the rows of W were split over work items (or the update is left to k_update_h): partial sums
-                    float* out = p.P + (size_t)(t / p.tiles_l) * p.split_stride + (size_t)l * (uint32_t)p.Kv;
+                    float* out = p.P + (size_t)sp * p.split_stride + (size_t)l * (uint32_t)p.ldH + koff;
                     #pragma unroll
                     for (int cc = 0; cc < FC::ACC; ++cc) {
                         const int c = h + NW * cc;
@@ -549,7 +512,8 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                     }
                 } else if (HSTEP) {
                     // H[:, n] <- H[:, n] .* (acc ./ max(sumW, EPS))  (col_divide + element_multiply, nmf.cu:142-145) + its TF32 pair
-                    const size_t base = (size_t)l * (uint32_t)p.Kv;
+                    const size_t base = (size_t)l * (uint32_t)p.ldH + koff;
+                    const float* sumW = p.sumW + koff;
                     #pragma unroll
                     for (int cc = 0; cc < FC::ACC; ++cc) {
                         const int c = h + NW * cc;
@@ -568,7 +532,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                                 #pragma unroll
                                 for (int jj = 0; jj < 16; ++jj) {
                                     const float a = acc[cc][hf * 16 + jj];
-                                    const float y = clampE(__ldg(p.sumW + c * 32 + hf * 16 + jj));    // 1 KB, L1-resident
+                                    const float y = clampE(__ldg(sumW + c * 32 + hf * 16 + jj));    // 1 KB, L1-resident
                                     float rc;
                                     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(y));
                                     const float q0 = a * rc;
@@ -577,7 +541,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                                 }
                                 if (!(qmax <= 1.0e30f)) {
                                     #pragma unroll
-                                    for (int jj = 0; jj < 16; ++jj) qv[jj] = acc[cc][hf * 16 + jj] / clampE(__ldg(p.sumW + c * 32 + hf * 16 + jj));
+                                    for (int jj = 0; jj < 16; ++jj) qv[jj] = acc[cc][hf * 16 + jj] / clampE(__ldg(sumW + c * 32 + hf * 16 + jj));
                                 }
                                 #pragma unroll
                                 for (int v = 0; v < 2; ++v) {
@@ -594,7 +558,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                         }
                     }
                 } else {
-                    float* out = p.P + (size_t)(t / p.tiles_l) * p.split_stride + l;
+                    float* out = p.P + (size_t)sp * p.split_stride + (size_t)koff * (uint32_t)p.ldP + l;
                     #pragma unroll
                     for (int cc = 0; cc < FC::ACC; ++cc) {
                         const int c = h + NW * cc;
@@ -612,6 +576,68 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
     __syncwarp();
     cluster_sync_all();
     if (warp == 1) { tc_fence_after(); tmem_dealloc_cg2(tmem_base, TMEM_COLS); }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side: one launch on CTA pairs, at most one pair per TPC, persistent over the work items
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+int num_sms_f() {
+    int dev = 0, n = 0;
+    CUDA_CHECK(cudaGetDevice(&dev));
+    CUDA_CHECK(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+    return n;
+}
+
+template <bool HSTEP, int NW, bool COST, int BN>
+void launch_fused_nw(const FusedParams& p, cudaStream_t st) {
+    // function attributes are per device: one host thread per GPU may launch the same instantiation
+    static std::atomic<unsigned long long> configured{0};            // bit d: done on device d
+    int dev = 0; CUDA_CHECK(cudaGetDevice(&dev));
+    if (!(configured.load(std::memory_order_acquire) >> (dev & 63) & 1ull)) {
+        CUDA_CHECK(cudaFuncSetAttribute(k_fused<HSTEP, NW, COST, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_BYTES));
+        configured.fetch_or(1ull << (dev & 63), std::memory_order_release);
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.blockDim = dim3(FCfg<NW>::NTHREADS, 1, 1);
+    cfg.dynamicSmemBytes = F_SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    static std::atomic<int> max_pairs{0};            // co-resident CTA pairs (one per TPC): 74 on B200 (same on every GPU of the box)
+    if (!max_pairs.load()) {
+        const int sms = num_sms_f();
+        cfg.gridDim = dim3(2u * (unsigned)(sms / 2), 1, 1);
+        int n = 0;
+        CUDA_CHECK(cudaOccupancyMaxActiveClusters(&n, k_fused<HSTEP, NW, COST, BN>, &cfg));
+        NMF_CHECK(n > 0, "no CTA pair of the fused half-iteration kernel fits on this device");
+        max_pairs.store(std::min(n, sms / 2));
+    }
+    const long long items = (long long)p.tiles_l * p.nsplit * p.nbatch;
+    cfg.gridDim = dim3(2u * (unsigned)std::min<long long>(items, max_pairs.load()), 1, 1);
+    CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_fused<HSTEP, NW, COST, BN>, p));
+    CUDA_CHECK_LAUNCH();
+}
+
+template <bool HSTEP, bool COST>
+void launch_fused_t(const FusedParams& p, cudaStream_t st) {
+    if (p.nw == 4) {
+        if (p.bn == F_BN_DB) launch_fused_nw<HSTEP, 4, COST, F_BN_DB>(p, st); else launch_fused_nw<HSTEP, 4, COST, F_BN>(p, st);
+    } else {
+        if (p.bn == F_BN_DB) launch_fused_nw<HSTEP, 2, COST, F_BN_DB>(p, st); else launch_fused_nw<HSTEP, 2, COST, F_BN>(p, st);
+    }
+}
+
+}  // namespace
+
+void launch_fused(bool hstep, bool cost, const FusedParams& p, cudaStream_t st) {
+    NMF_CHECK(p.nw == 2 || (p.nw == 4 && p.Kv <= 128), "fused kernel: 4 worker warps per quadrant need a P tile of <= 128 columns");
+    NMF_CHECK(!cost || hstep, "fused kernel: only the H step carries the cost");
+    if (hstep) { if (cost) launch_fused_t<true, true>(p, st); else launch_fused_t<true, false>(p, st); }
+    else launch_fused_t<false, false>(p, st);
 }
 
 }}  // namespace nmf::umma

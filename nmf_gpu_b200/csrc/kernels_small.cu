@@ -185,7 +185,7 @@ __global__ void __launch_bounds__(256) k_update_w(float* __restrict__ W, float* 
 // H update from split partial sums of W'*Y (small problems: the H GEMM is split over the rows of W so
 // that it fills the SMs): H <- H .* ((sum_s P[s]) ./ max(sumW,EPS)), ordered sum, emits the TF32 pair.
 // One thread per 4 consecutive k of one column (float4; Kv is a multiple of 32).
-// ROWSUM (Kv in {64, 128, 256}: every thread keeps the same 4 rows k over its grid-stride loop): the block also emits
+// ROWSUM (Kv divides 1024: every thread keeps the same 4 rows k over its grid-stride loop): the block also emits
 // its partial row sums of the NEW H, rs_partials[block][k] (refcompat: only the columns of the reference's subsample),
 // so that the W half needs no pass of its own over H: k_rowsum_finish2 folds the blocks in a fixed order.
 template <bool ROWSUM>
@@ -265,6 +265,8 @@ __global__ void __launch_bounds__(1024) k_sum_partials(const double* __restrict_
     // one block; thread-strided ordered sums, a fixed shuffle tree per warp, then warp 0 over the 32 warp sums:
     // deterministic (no atomics), and wide enough for the ~1e5 per-warp partials of the fused H step
     __shared__ double wsum[32];
+    partials += (size_t)blockIdx.x * n;                       // one block per batch entry (restart)
+    out += blockIdx.x;
     double s = 0.0;
     for (int i = threadIdx.x; i < n; i += 1024) s += partials[i];
     #pragma unroll
@@ -276,6 +278,15 @@ __global__ void __launch_bounds__(1024) k_sum_partials(const double* __restrict_
         #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
         if (threadIdx.x == 0) *out = s;
+    }
+}
+
+__global__ void k_gather_rows(const float* __restrict__ src, int ld, int cols, const int* __restrict__ rows, int count,
+                              float* __restrict__ dst) {
+    const size_t total = (size_t)cols * count;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const size_t j = e / count; const int i = (int)(e - j * count);
+        dst[e] = src[j * (size_t)ld + rows[i]];
     }
 }
 
@@ -351,7 +362,7 @@ int launch_update_h(float* H, float* Hhi, float* Hlo, const float* P, int nsplit
                     const float* sumW, const Dims& d, cudaStream_t st, float* rowsum_partials) {
     const size_t total4 = (size_t)d.Kv * d.Nv / 4;
     const int grid = grid_for(total4, 256);
-    const bool rowsum = rowsum_partials != nullptr && (d.Kv == 64 || d.Kv == 128 || d.Kv == 256);
+    const bool rowsum = rowsum_partials != nullptr && d.Kv <= 1024 && 1024 % d.Kv == 0;   // every thread keeps the same 4 rows k over its loop
     if (rowsum) k_update_h<true><<<grid, 256, 0, st>>>(H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4, rowsum_partials, d.n_offset, d.refcompat);
     else        k_update_h<false><<<grid, 256, 0, st>>>(H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4, nullptr, 0, 0);
     CUDA_CHECK_LAUNCH();
@@ -363,13 +374,19 @@ void launch_rowsum_finish2(const float* partials, float* sumH, int nblocks, cons
     CUDA_CHECK_LAUNCH();
 }
 
+void launch_gather_rows(const float* src, int ld, int cols, const int* rows, int count, float* dst, cudaStream_t st) {
+    if ((size_t)cols * count == 0) return;
+    k_gather_rows<<<grid_for((size_t)cols * count, 256), 256, 0, st>>>(src, ld, cols, rows, count, dst);
+    CUDA_CHECK_LAUNCH();
+}
+
 void launch_fold_splits(const float* P, int nsplit, size_t split_stride, float* out, size_t n, cudaStream_t st) {
     k_fold_splits<<<grid_for(n / 4, 256), 256, 0, st>>>(P, nsplit, split_stride, out, n / 4);
     CUDA_CHECK_LAUNCH();
 }
 
-void launch_sum_partials(const double* partials, int n, double* out, cudaStream_t st) {
-    k_sum_partials<<<1, 1024, 0, st>>>(partials, n, out);
+void launch_sum_partials(const double* partials, int n, int nbatch, double* out, cudaStream_t st) {
+    k_sum_partials<<<nbatch, 1024, 0, st>>>(partials, n, out);
     CUDA_CHECK_LAUNCH();
 }
 

@@ -1,18 +1,47 @@
 // session.hpp — one rank's device-resident NMF problem and the iteration driver.
 #pragma once
+#include <vector>
+
 #include "common.hpp"
 
 namespace nmf {
 
-namespace umma { struct Plan; }
+namespace umma {
+struct Plan;
+// Tuning / A-B switches of the tcgen05 engine (NMF_UMMA_* environment variables): read ONCE when a session is created
+// (read_tuning) and carried by it — no getenv on any launch path.
+struct Tuning {
+    int pair = 1;          // NMF_UMMA_PAIR      CTA pairs (cta_group::2) wherever the output has > 128 rows
+    int chunk = 4;         // NMF_UMMA_CHUNK     32-deep blocks accumulated in TMEM between round-to-nearest promotions (1..16)
+    int w3_max_k = 192;    // NMF_UMMA_W3_MAXK   whole-tile kernels: 12 epilogue warps up to this reduction length
+    int hint_h = 0;        // NMF_UMMA_HINT_H    L2 eviction priority of the H operand
+    int np_bn_cap = 256;   // NMF_UMMA_NP_BNCAP  width cap of one-CTA tiles of the chunked kernels
+    int hints = 1;         // NMF_UMMA_HINTS     L2 eviction-priority hints on the operand / epilogue streams
+    int xpf = 0;           // NMF_UMMA_XPF       G1: L2 prefetch of X two chunks ahead
+    int fuse = 1;          // NMF_UMMA_FUSE      0 never fuse a half-iteration, 1/2 whenever the shape allows
+    int fuse_steps = 3;    // NMF_UMMA_FUSE_STEPS bit 0 W step, bit 1 H step
+    int fhsplit = 0;       // NMF_UMMA_FHSPLIT   forced row-split count of the fused H step (0: the cost model chooses)
+    int fuse_nw = 0;       // NMF_UMMA_FUSE_NW   worker warps per TMEM quadrant of the fused kernels (0: 4 when Kv <= 128, else 2)
+    int fh_defer = 0;      // NMF_UMMA_FH_DEFER  fused H step leaves the update to k_update_h even without a row split
+    int fuse_bn = 128;     // NMF_UMMA_FUSE_BN   S tile width of the fused kernels (128 double-buffered, or 256)
+    int hsplit = 0;        // NMF_UMMA_HSPLIT    forced row-split count of the two-kernel H update (0: automatic)
+    int keep_quotient = 0; // NMF_KEEP_QUOTIENT  allocate the M x N quotient buffer even when both half-iterations are fused
+    int variant = 0;       // NMF_UMMA_VARIANT   bring-up / timing switches that give WRONG results: honoured only by diagnostic
+                           //                    builds (NMF_BUILD_DIAG=1 -> -DNMF_DIAG); a release build ignores the variable
+    int pad64 = 1;         // NMF_PAD_K64        exact semantics: pad K to a multiple of 64 when that lets the half-iterations fuse
+};
+Tuning read_tuning();
+}
 
 struct Nccl;   // dlopen'ed NCCL entry points + communicator (dist.cpp)
 
 struct nmf_session_impl {
     nmf_options opt{};
+    umma::Tuning tune{};
     Dims d{};
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;            // H2D of X in column blocks (created on first use)
 
     // fp32 masters (column-major, ld = Mv / Kv)
     float *W = nullptr, *H = nullptr, *X = nullptr;
@@ -32,7 +61,11 @@ struct nmf_session_impl {
     double *cost_partials = nullptr; int n_cost_partials = 0;
     int n_cost_partials_fused = 0;                // partials of the fused H step's cost variant (0: that step is not fused)
     float *Hbak = nullptr;                        // H before a fused H step that carries the cost (allocated on first use)
-    double *cost_dev = nullptr, *cost_host = nullptr /* pinned */;
+    double *cost_dev = nullptr, *cost_host = nullptr /* pinned */;   // R values each
+    // restarts (d.R > 1): per-restart state of the last run; a restart that met the threshold at a check is retired — its
+    // factors of that moment are kept in Wfin / Hfin and put back when the run ends
+    std::vector<double> costs; std::vector<int> iters_r; std::vector<char> conv_r, retired;
+    float *Wfin = nullptr, *Hfin = nullptr;
 
     umma::Plan* plan = nullptr;
 
@@ -44,7 +77,7 @@ struct nmf_session_impl {
     long long launches_full = 0, launches_rest = 0, launches_head = 0;
     long long launches = 0;    // running count of this library's kernel launches
 
-    ~nmf_session_impl();
+    virtual ~nmf_session_impl();
 };
 
 // phases for t[10]
@@ -65,15 +98,17 @@ void nccl_join(nmf_session_impl& s, int rank, int nranks, const void* id128);
 void nccl_allreduce_f32(nmf_session_impl& s, float* buf, size_t n);
 void nccl_allreduce_f64(nmf_session_impl& s, double* buf, size_t n);
 void nccl_destroy(Nccl* n);
+void nccl_init_all(nmf_session_impl* const* sessions, int g);   // one process, a session per GPU: ncclCommInitAll
+void nccl_abort(nmf_session_impl& s);                           // unblock peers of a failed rank (ncclCommAbort)
 void nccl_share(nmf_session_impl& dst, nmf_session_impl& src);
 
 namespace umma {
 // tcgen05 engine (kernels_umma.cu)
 Plan* plan_create(nmf_session_impl& s);
 void  plan_destroy(Plan* p);
-int   cost_partial_count(const Dims& d);
-int   numer_splits(const Dims& d);
-int   updh_splits(const Dims& d);
+int   cost_partial_count(const Dims& d, const Tuning& tn);
+int   numer_splits(const Dims& d, const Tuning& tn);
+int   updh_splits(const Dims& d, const Tuning& tn);
 void  quotient(nmf_session_impl& s, bool with_cost);
 void  update_h(nmf_session_impl& s);
 void  numer(nmf_session_impl& s);
@@ -83,11 +118,12 @@ void  fused_w(nmf_session_impl& s);
 // fused H step: first quotient + W'*Y + the H update in one kernel (needs sumW)
 bool  fused_h_enabled(const nmf_session_impl& s);
 int   fused_h(nmf_session_impl& s, bool with_cost = false);   // returns the kernels launched (2 when the rows of W are split)
-int   fused_h_splits(const Dims& d, int passes);
-int   fused_cost_partial_count(const Dims& d, int passes);
-bool  fused_both_wanted(const Dims& d, int passes);
+int   fused_h_splits(const Dims& d, int passes, const Tuning& tn);
+int   fused_cost_partial_count(const Dims& d, int passes, const Tuning& tn);   // per restart
+bool  fused_both_wanted(const Dims& d, int passes, const Tuning& tn);
+bool  fused_shape_ok(int Kr, int passes, const Tuning& tn);   // Kr (one restart's padded K) is a multiple of 64 and <= 256
 unsigned int protocol_error(const nmf_session_impl& s);
-bool  fused_h_needs_part(const Dims& d, int passes);   // the fused H step writes partial sums (row split or deferred update)
+bool  fused_h_needs_part(const Dims& d, int passes, const Tuning& tn);   // the fused H step writes partial sums (row split or deferred update)
 // raw contraction for descriptor bring-up (nmf_dbg_gemm)
 void  dbg_gemm(int which, const float* dA, const float* dB, float* dC, int M, int N, int K, int passes,
                cudaStream_t st);

@@ -337,6 +337,15 @@ int nmf_oracle_threads(void) {
 #endif
 }
 
+// OpenMP threads for every later call (torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU baseline wants them all).
+void nmf_oracle_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 float nmf_oracle_eps(void) { return kEps; }
 
 // Full update_div on host arrays (column-major, unpadded: W MxK, H KxN, X MxN), in place on W, H.

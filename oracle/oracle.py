@@ -34,6 +34,8 @@ def lib():
             _lib = ctypes.CDLL(_LIB)
         L = _lib
         L.nmf_oracle_threads.restype = ctypes.c_int
+        L.nmf_oracle_set_threads.restype = None
+        L.nmf_oracle_set_threads.argtypes = [ctypes.c_int]
         L.nmf_oracle_eps.restype = ctypes.c_float
         L.nmf_oracle_update_div.restype = ctypes.c_int
         L.nmf_oracle_update_div.argtypes = [_f32p, _f32p, _f32p] + [ctypes.c_int] * 3 + [
@@ -114,3 +116,8 @@ def time_iterations(W, H, X, iters):
 
 def threads():
     return lib().nmf_oracle_threads()
+
+
+def set_threads(n):
+    """OpenMP threads for every later call (torchrun exports OMP_NUM_THREADS=1 to its workers)."""
+    lib().nmf_oracle_set_threads(int(n))

@@ -1,5 +1,6 @@
 """Multi-GPU parity (run under torchrun on N GPUs): the column-sharded run must reproduce the
-single-GPU run of the same problem (differences come only from reduction order).
+single-GPU run of the same problem (differences come only from reduction order) AND the fp64 CPU oracle
+(exact semantics, the north-star tolerance for this iteration count).
     python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tests/dist_gpu_parity.py
 Prints one PARITY line on rank 0 and exits non-zero on failure."""
 import json
@@ -61,10 +62,16 @@ def main():
                 cost1 = s1.cost()
             out[mode] = dict(W=max_rel(Wd, W1), H=max_rel(Hm, H1), cost_rel=abs(cost - cost1) / abs(cost1),
                              iters=(res.iterations, r1.iterations), fused_steps=fused)
+            if mode == "exact":                                   # and against the oracle, not only against ourselves
+                from oracle import oracle
+                Wo, Ho, _, costo = oracle.update_div(W, H, X, 0.0, iters, "exact", acc64=True)
+                out[mode].update(W_vs_oracle=max_rel(Wd, Wo), H_vs_oracle=max_rel(Hm, Ho),
+                                 cost_vs_oracle=abs(cost - costo) / abs(costo))
     ok = True
     if rank == 0:
         print("PARITY " + json.dumps(dict(world=world, **out)), flush=True)
         ok = all(v["W"] < 2e-5 and v["H"] < 2e-5 and v["cost_rel"] < 1e-5 and v["iters"][0] == v["iters"][1]
+                 and v["W_vs_oracle"] < 1e-4 and v["H_vs_oracle"] < 1e-4 and v["cost_vs_oracle"] < 1e-5
                  for k, v in out.items() if k == "exact")
         ok &= out["refcompat"]["cost_rel"] < 1e-5
     dist.destroy_process_group()
