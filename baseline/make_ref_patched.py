@@ -7,8 +7,8 @@ dimensions above 65536 (cuda/nmf.cu:59-70), byte and element counts are 32-bit (
 col_div puts the column count into grid.y (<= 65535, :240), row_div launches rows_padded threads per block (:212-217),
 an inverted assert fires when K_p < 128 (:287,406), and its row/column sums read stale shared memory (:676-683,
 :724-731).  Nothing of the reference is copied into the repository: this script reads /root/reference/cuda/*.cu|cuh|hpp
-where they lie, applies the textual patches below IN MEMORY, writes the patched sources to the git-ignored
-baseline/_ref/src/ and compiles them there.  Every patch asserts that the text it replaces is present, so a different
+where they lie, applies the textual patches below IN MEMORY, writes the patched sources to a temporary directory outside
+the tree, compiles them into the git-ignored baseline/_ref/ and deletes them again.  Every patch asserts that the text it replaces is present, so a different
 reference revision fails loudly instead of building something else.
 
 Patches (all in the spirit of "what the authors meant", i.e. the `exact` semantics of DESIGN.md):
@@ -26,8 +26,10 @@ usage: make_ref_patched.py [--ref /root/reference] [--out baseline/_ref]
 """
 import argparse
 import os
+import shutil
 import subprocess
 import sys
+import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 
@@ -163,13 +165,15 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--ref", default="/root/reference")
     ap.add_argument("--out", default=os.path.join(HERE, "_ref"))
+    ap.add_argument("--keep-src", action="store_true", help="leave the patched sources in their temporary directory (to read the diff)")
     a = ap.parse_args()
     src = os.path.join(a.ref, "cuda")
     if not os.path.isdir(src):
         print(f"make_ref_patched: {src} absent - keeping any prebuilt {a.out}/nmf_ref_patched")
         return 0
-    out_src = os.path.join(a.out, "src")
-    os.makedirs(out_src, exist_ok=True)
+    os.makedirs(a.out, exist_ok=True)
+    out_src = tempfile.mkdtemp(prefix="nmf_ref_patched_")      # the patched sources live only while nvcc runs: nothing of the
+                                                               # reference's text stays in the tree, only the binary
     rd = lambda f: open(os.path.join(src, f)).read()
     files = {"matrix.cu": patch_matrix_cu(rd("matrix.cu")), "nmf.cu": patch_nmf_cu(rd("nmf.cu")),
              "matrix.cuh": rd("matrix.cuh"), "error-check.hpp": rd("error-check.hpp")}
@@ -181,8 +185,12 @@ def main():
     cmd = [os.path.join(cuda, "bin", "nvcc"), "-gencode", "arch=compute_100,code=sm_100", "-O3", "-DNDEBUG", "-ccbin", "/usr/bin/g++",
            "-I" + out_src, "-L" + os.path.join(cuda, "lib64"), "-L" + os.path.join(cuda, "lib64", "stubs"),
            "-o", exe, os.path.join(out_src, "nmf.cu"), os.path.join(out_src, "matrix.cu"), "-lcublas", "-lcudart", "-lcuda"]
-    subprocess.check_call(cmd)
-    print(exe)
+    try:
+        subprocess.check_call(cmd)
+    finally:
+        if not a.keep_src:
+            shutil.rmtree(out_src, ignore_errors=True)
+    print(exe + (f"  (patched sources kept in {out_src})" if a.keep_src else ""))
     return 0
 
 
