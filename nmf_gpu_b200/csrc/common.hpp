@@ -33,6 +33,39 @@ struct Error : std::runtime_error {
                 cudaGetErrorString(e__), (int)e__); } while (0)
 #define CUDA_CHECK_LAUNCH() CUDA_CHECK(cudaGetLastError())
 
+// Programmatic dependent launch (PDL): the kernels of an iteration are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, so a kernel's CTAs are scheduled as the SMs of its predecessor
+// drain and its prologue (barrier init, TMEM allocation, tensor-map prefetch) overlaps the predecessor's tail; every kernel
+// executes griddepcontrol.wait before it touches global memory.  Thread-local switch: the session driver turns it on
+// around its launches (NMF_PDL=0 turns it off), everything else launches plainly.
+void set_launch_pdl(bool on);
+bool launch_pdl();
+
+// cudaLaunchKernelEx with the PDL attribute when the switch is on
+template <typename... KArgs, typename... Args>
+void launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    if (launch_pdl()) {
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+    }
+    cudaError_t e__ = cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+    if (e__ != cudaSuccess) ::nmf::fail(__FILE__, __LINE__, std::string("cudaLaunchKernelEx: ") + cudaGetErrorName(e__) + " - " + cudaGetErrorString(e__), (int)e__);
+    e__ = cudaGetLastError();
+    if (e__ != cudaSuccess) ::nmf::fail(__FILE__, __LINE__, std::string("kernel launch: ") + cudaGetErrorName(e__) + " - " + cudaGetErrorString(e__), (int)e__);
+}
+#ifdef __CUDACC__
+// first statements of every iteration kernel: wait for the predecessor grid (no-op without the launch attribute), then
+// let the successor's CTAs be scheduled as this grid's SMs drain
+__device__ __forceinline__ void pdl_sync() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+#endif
+
 inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 inline long long round_up_ll(long long v, long long m) { return (v + m - 1) / m * m; }
 
@@ -96,8 +129,15 @@ void launch_rowsum(const float* H, float* partials, float* sumH, const Dims& d, 
 
 // W[m,k] <- W[m,k] * ((sum_s P[s][m,k]) / max(sumH[k],EPS))   (reference: row_divide + element_multiply,
 // cuda/nmf.cu:172-175).  The divide is skipped when !d.w_divide.  Optionally writes the TF32 split.
-void launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nsplit, size_t split_stride,
-                     const float* sumH, const Dims& d, cudaStream_t st);
+// Small problems (the launch count matters more than the bytes): one block per column k, which can also
+//   fold the `rs_blocks` partial row sums of the new H that the H update left (rs_partials != nullptr) into sumH[k] first, and
+//   emit sumW[k] = the column sum of the NEW W (what the next H step divides by; refcompat: the subsample) when sumW_out != nullptr
+// — then neither the row-sum finish nor the column-sum kernel runs.  Returns true when sumW_out was written.
+bool launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nsplit, size_t split_stride,
+                     float* sumH, const Dims& d, cudaStream_t st,
+                     const float* rs_partials = nullptr, int rs_blocks = 0, float* sumW_out = nullptr);
+// whether launch_update_w will run the one-block-per-column kernel for this shape (the caller may then skip the row-sum finish)
+bool update_w_by_column(const Dims& d, int nsplit);
 
 // dst[j*count + i] = src[j*ld + rows[i]] for j < cols (rows = device array of `count` row indices): sampled rows of a
 // column-major matrix, for the spot checks of full-size runs

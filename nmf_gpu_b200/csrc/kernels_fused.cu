@@ -125,6 +125,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t tmem_S = tmem_base, tmem_P = tmem_base + (uint32_t)F_BN;
+    pdl_sync();            // everything above overlapped the predecessor's tail; global memory is touched only from here on
     // one opaque 32-bit shared-space base; every ring slot and barrier below is this plus a constant (see umma_ptx.cuh)
     uint32_t sb = smem_u32(smem);
     asm volatile("" : "+r"(sb));
@@ -603,10 +604,15 @@ void launch_fused_nw(const FusedParams& p, cudaStream_t st) {
     cfg.blockDim = dim3(FCfg<NW>::NTHREADS, 1, 1);
     cfg.dynamicSmemBytes = F_SMEM_BYTES;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
+    if (launch_pdl()) {
+        attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[1].val.programmaticStreamSerializationAllowed = 1;
+        cfg.numAttrs = 2;
+    }
     static std::atomic<int> max_pairs{0};            // co-resident CTA pairs (one per TPC): 74 on B200 (same on every GPU of the box)
     if (!max_pairs.load()) {
         const int sms = num_sms_f();

@@ -7,6 +7,10 @@
 
 namespace nmf {
 
+namespace { thread_local bool t_pdl = false; }
+void set_launch_pdl(bool on) { t_pdl = on; }
+bool launch_pdl() { return t_pdl; }
+
 namespace {
 
 __device__ __forceinline__ float clampE(float v) { return v < NMF_EPS_F ? NMF_EPS_F : v; }
@@ -100,6 +104,7 @@ __global__ void k_split_tf32(const float* __restrict__ x, float* __restrict__ hi
 // R1: one block per column of W (contiguous, coalesced), 256 threads, shuffle tree.
 __global__ void __launch_bounds__(256) k_colsum(const float* __restrict__ W, float* __restrict__ sumW,
                                                 int Mv, int ld, int refcompat) {
+    pdl_sync();
     const float* col = W + (size_t)blockIdx.x * ld;
     float s = 0.0f;
     if (refcompat) {
@@ -118,33 +123,52 @@ __global__ void __launch_bounds__(256) k_colsum(const float* __restrict__ W, flo
     }
 }
 
-// R2 pass 1: block = 32 (rows k, contiguous => coalesced 128 B per warp) x 8 (column lanes);
-// each block covers kRowsumChunk columns.  partial[chunk][k].
+// R2 pass 1: a block is KX threads along k (each owns 4 consecutive rows k: one 16-byte load per column, the KX threads of
+// a column read KX*16 contiguous bytes) x NY column lanes, and covers kRowsumChunk columns; every thread keeps 4 independent
+// float4 accumulators, i.e. 64 bytes in flight (with one scalar load in flight per thread the kernel ran at 54 % of the
+// HBM peak: latency-, not bandwidth-bound).  partial[chunk][k]; fixed summation order.
 constexpr int kRowsumChunk = 512;
 __global__ void __launch_bounds__(256) k_rowsum_partial(const float* __restrict__ H, float* __restrict__ partials,
                                                         int Kv, int Nv, long long n_offset, int refcompat) {
-    const int k = blockIdx.x * 32 + threadIdx.x;
+    pdl_sync();
+    const int KX = blockDim.x, NY = blockDim.y;
+    const int k4 = blockIdx.x * KX + threadIdx.x;              // float4 index along k
+    const bool k_ok = 4 * k4 < Kv;
     const int n0 = blockIdx.y * kRowsumChunk;
     const int n1 = min(Nv, n0 + kRowsumChunk);
-    float s = 0.0f;
-    if (k < Kv) {
-        for (int n = n0 + threadIdx.y; n < n1; n += 8) {
-            if (!refcompat || ref_sum_mask(n_offset + n)) s += H[(size_t)n * Kv + k];
+    float4 a[4];
+    #pragma unroll
+    for (int u = 0; u < 4; ++u) a[u] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (k_ok) {
+        const float4* Hp = reinterpret_cast<const float4*>(H) + k4;
+        const size_t ld4 = (size_t)(Kv >> 2);
+        for (int n = n0 + threadIdx.y; n < n1; n += 4 * NY) {
+            float4 v[4];
+            #pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int nn = n + u * NY;
+                const bool take = nn < n1 && (!refcompat || ref_sum_mask(n_offset + nn));
+                v[u] = take ? Hp[(size_t)nn * ld4] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            }
+            #pragma unroll
+            for (int u = 0; u < 4; ++u) { a[u].x += v[u].x; a[u].y += v[u].y; a[u].z += v[u].z; a[u].w += v[u].w; }
         }
     }
-    __shared__ float sm[8][33];
-    sm[threadIdx.y][threadIdx.x] = s;
+    __shared__ float4 sm[256];
+    float4 t;
+    t.x = (a[0].x + a[1].x) + (a[2].x + a[3].x); t.y = (a[0].y + a[1].y) + (a[2].y + a[3].y);
+    t.z = (a[0].z + a[1].z) + (a[2].z + a[3].z); t.w = (a[0].w + a[1].w) + (a[2].w + a[3].w);
+    sm[threadIdx.y * KX + threadIdx.x] = t;
     __syncthreads();
-    if (threadIdx.y == 0 && k < Kv) {
-        float t = 0.0f;
-        #pragma unroll
-        for (int j = 0; j < 8; ++j) t += sm[j][threadIdx.x];
-        partials[(size_t)blockIdx.y * Kv + k] = t;
+    if (threadIdx.y == 0 && k_ok) {
+        for (int j = 1; j < NY; ++j) { const float4 v = sm[j * KX + threadIdx.x]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
+        *reinterpret_cast<float4*>(partials + (size_t)blockIdx.y * Kv + 4 * k4) = t;
     }
 }
 
 // R2 pass 2: ordered sum over the chunks.
 __global__ void k_rowsum_finish(const float* __restrict__ partials, float* __restrict__ sumH, int Kv, int nchunks) {
+    pdl_sync();
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= Kv) return;
     float s = 0.0f;
@@ -156,6 +180,7 @@ __global__ void k_rowsum_finish(const float* __restrict__ partials, float* __res
 __global__ void __launch_bounds__(256) k_update_w(float* __restrict__ W, float* __restrict__ Whi, float* __restrict__ Wlo,
                                                   const float* __restrict__ P, int nsplit, size_t split_stride,
                                                   const float* __restrict__ sumH, int Mv, int Kv, int divide) {
+    pdl_sync();
     const size_t total4 = (size_t)Mv * Kv / 4;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
         const size_t e = i * 4;
@@ -182,6 +207,62 @@ __global__ void __launch_bounds__(256) k_update_w(float* __restrict__ W, float* 
     }
 }
 
+// W update, one block per column k (small problems: fewer launches).  Deterministic: thread-strided partial sums, a fixed
+// shuffle tree per warp, then warp 0 over the warp sums.
+__device__ __forceinline__ float block_sum_512(float v, float* red) {      // every thread returns the block's sum
+    v = warp_sum(v);
+    __syncthreads();                                     // `red` may still be read from a previous call
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float t = (threadIdx.x & 31) < 16 ? red[threadIdx.x & 31] : 0.0f;
+    return warp_sum(t);
+}
+__global__ void __launch_bounds__(512) k_update_w_col(float* __restrict__ W, float* __restrict__ Whi, float* __restrict__ Wlo,
+                                                      const float* __restrict__ P, int nsplit, size_t split_stride,
+                                                      float* __restrict__ sumH, const float* __restrict__ rs_partials, int rs_blocks,
+                                                      int Mv, int Kv, int divide, float* __restrict__ sumW, int refcompat) {
+    pdl_sync();
+    __shared__ float red[16];
+    const int k = blockIdx.x;
+    float d;
+    if (rs_partials != nullptr) {                        // sum_rows of the new H (nmf.cu:164): ordered fold of the H update's partials
+        float s = 0.0f;
+        for (int c = threadIdx.x; c < rs_blocks; c += 512) s += rs_partials[(size_t)c * Kv + k];
+        s = block_sum_512(s, red);
+        if (threadIdx.x == 0) sumH[k] = s;
+        d = clampE(s);
+    } else d = clampE(sumH[k]);
+    float cs = 0.0f;
+    const size_t col = (size_t)k * Mv;
+    for (int m = 4 * threadIdx.x; m < Mv; m += 4 * 512) {
+        const size_t e = col + m;
+        float4 acc = *reinterpret_cast<const float4*>(P + e);
+        for (int s = 1; s < nsplit; ++s) {                       // ordered: split 0,1,2,...
+            const float4 p = *reinterpret_cast<const float4*>(P + (size_t)s * split_stride + e);
+            acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+        }
+        if (divide) { acc.x = acc.x / d; acc.y = acc.y / d; acc.z = acc.z / d; acc.w = acc.w / d; }   // row_div, cuda/matrix.cu:220-224
+        float4 w = *reinterpret_cast<float4*>(W + e);
+        w.x *= acc.x; w.y *= acc.y; w.z *= acc.z; w.w *= acc.w;  // vec_mul, cuda/matrix.cu:174-180
+        *reinterpret_cast<float4*>(W + e) = w;
+        if (Whi != nullptr) {
+            float4 h, l;
+            tf32_split(w.x, h.x, l.x); tf32_split(w.y, h.y, l.y);
+            tf32_split(w.z, h.z, l.z); tf32_split(w.w, h.w, l.w);
+            *reinterpret_cast<float4*>(Whi + e) = h;
+            *reinterpret_cast<float4*>(Wlo + e) = l;
+        }
+        if (refcompat) {                                         // the reference's stale-read tail: rows m mod 64 in {0,1,2,4,8,16,32}
+            cs += (ref_sum_mask(m) ? w.x : 0.0f) + (ref_sum_mask(m + 1) ? w.y : 0.0f) + (ref_sum_mask(m + 2) ? w.z : 0.0f) +
+                  (ref_sum_mask(m + 3) ? w.w : 0.0f);
+        } else cs += (w.x + w.y) + (w.z + w.w);
+    }
+    if (sumW != nullptr) {                                       // sum_cols of the new W (nmf.cu:134 of the NEXT iteration)
+        cs = block_sum_512(cs, red);
+        if (threadIdx.x == 0) sumW[k] = cs;
+    }
+}
+
 // H update from split partial sums of W'*Y (small problems: the H GEMM is split over the rows of W so
 // that it fills the SMs): H <- H .* ((sum_s P[s]) ./ max(sumW,EPS)), ordered sum, emits the TF32 pair.
 // One thread per 4 consecutive k of one column (float4; Kv is a multiple of 32).
@@ -193,6 +274,7 @@ __global__ void __launch_bounds__(256) k_update_h(float* __restrict__ H, float* 
                                                   const float* __restrict__ P, int nsplit, size_t split_stride,
                                                   const float* __restrict__ sumW, int Kv, size_t total4,
                                                   float* __restrict__ rs_partials, long long n_offset, int refcompat) {
+    pdl_sync();
     float4 rs = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
         const size_t e = i * 4;
@@ -235,6 +317,7 @@ __global__ void __launch_bounds__(256) k_update_h(float* __restrict__ H, float* 
 
 // ordered fold of per-block partial row sums: block = 32 rows k x 32 groups; group g sums blocks g, g + 32, ..
 __global__ void __launch_bounds__(1024) k_rowsum_finish2(const float* __restrict__ partials, float* __restrict__ sumH, int Kv, int nblocks) {
+    pdl_sync();
     __shared__ float sm[32][33];
     const int k = blockIdx.x * 32 + threadIdx.x;
     float s = 0.0f;
@@ -251,6 +334,7 @@ __global__ void __launch_bounds__(1024) k_rowsum_finish2(const float* __restrict
 
 __global__ void __launch_bounds__(256) k_fold_splits(const float* __restrict__ P, int nsplit, size_t split_stride,
                                                      float* __restrict__ out, size_t n4) {
+    pdl_sync();
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
         float4 acc = *reinterpret_cast<const float4*>(P + i * 4);
         for (int s = 1; s < nsplit; ++s) {
@@ -262,6 +346,7 @@ __global__ void __launch_bounds__(256) k_fold_splits(const float* __restrict__ P
 }
 
 __global__ void __launch_bounds__(1024) k_sum_partials(const double* __restrict__ partials, int n, double* __restrict__ out) {
+    pdl_sync();
     // one block; thread-strided ordered sums, a fixed shuffle tree per warp, then warp 0 over the 32 warp sums:
     // deterministic (no atomics), and wide enough for the ~1e5 per-warp partials of the fused H step
     __shared__ double wsum[32];
@@ -332,8 +417,7 @@ void launch_split_tf32(const float* x, float* hi, float* lo, size_t n, cudaStrea
 }
 
 void launch_colsum(const float* W, float* sumW, const Dims& d, cudaStream_t st) {
-    k_colsum<<<d.Kv, 256, 0, st>>>(W, sumW, d.Mv, d.Mv, d.refcompat);
-    CUDA_CHECK_LAUNCH();
+    launch_k(k_colsum, dim3(d.Kv), dim3(256), 0, st, W, sumW, d.Mv, d.Mv, d.refcompat);
 }
 
 int rowsum_partial_count(const Dims& d) {
@@ -344,18 +428,26 @@ int rowsum_partial_count(const Dims& d) {
 
 void launch_rowsum(const float* H, float* partials, float* sumH, const Dims& d, cudaStream_t st) {
     const int nch = (d.Nv + kRowsumChunk - 1) / kRowsumChunk;
-    dim3 grid((d.Kv + 31) / 32, nch), block(32, 8);
-    k_rowsum_partial<<<grid, block, 0, st>>>(H, partials, d.Kv, d.Nv, d.n_offset, d.refcompat);
-    CUDA_CHECK_LAUNCH();
-    k_rowsum_finish<<<(d.Kv + 127) / 128, 128, 0, st>>>(partials, sumH, d.Kv, nch);
-    CUDA_CHECK_LAUNCH();
+    const int KX = std::min(d.Kv / 4, 64), NY = 256 / KX;
+    dim3 grid((d.Kv / 4 + KX - 1) / KX, nch), block(KX, NY);
+    launch_k(k_rowsum_partial, grid, block, 0, st, H, partials, d.Kv, d.Nv, d.n_offset, d.refcompat);
+    launch_k(k_rowsum_finish, dim3((d.Kv + 127) / 128), dim3(128), 0, st, (const float*)partials, sumH, d.Kv, nch);
 }
 
-void launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nsplit, size_t split_stride,
-                     const float* sumH, const Dims& d, cudaStream_t st) {
-    k_update_w<<<grid_for(d.szW() / 4, 256), 256, 0, st>>>(W, Whi, Wlo, P, nsplit, split_stride, sumH,
-                                                           d.Mv, d.Kv, d.w_divide);
-    CUDA_CHECK_LAUNCH();
+// the one-block-per-column kernel pays when the launch count matters more than the bytes: up to 64 MB of partials + W
+bool update_w_by_column(const Dims& d, int nsplit) { return d.szW() * (size_t)(nsplit + 4) * 4 <= ((size_t)64 << 20); }
+
+bool launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nsplit, size_t split_stride,
+                     float* sumH, const Dims& d, cudaStream_t st, const float* rs_partials, int rs_blocks, float* sumW_out) {
+    if (update_w_by_column(d, nsplit)) {
+        launch_k(k_update_w_col, dim3(d.Kv), dim3(512), 0, st, W, Whi, Wlo, P, nsplit, split_stride, sumH, rs_partials, rs_blocks,
+                 d.Mv, d.Kv, d.w_divide, sumW_out, d.refcompat);
+        return sumW_out != nullptr;
+    }
+    NMF_CHECK(rs_partials == nullptr, "launch_update_w: fold the row-sum partials first for this shape");
+    launch_k(k_update_w, dim3(grid_for(d.szW() / 4, 256)), dim3(256), 0, st, W, Whi, Wlo, P, nsplit, split_stride, (const float*)sumH,
+             d.Mv, d.Kv, d.w_divide);
+    return false;
 }
 
 int launch_update_h(float* H, float* Hhi, float* Hlo, const float* P, int nsplit, size_t split_stride,
@@ -363,15 +455,13 @@ int launch_update_h(float* H, float* Hhi, float* Hlo, const float* P, int nsplit
     const size_t total4 = (size_t)d.Kv * d.Nv / 4;
     const int grid = grid_for(total4, 256);
     const bool rowsum = rowsum_partials != nullptr && d.Kv <= 1024 && 1024 % d.Kv == 0;   // every thread keeps the same 4 rows k over its loop
-    if (rowsum) k_update_h<true><<<grid, 256, 0, st>>>(H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4, rowsum_partials, d.n_offset, d.refcompat);
-    else        k_update_h<false><<<grid, 256, 0, st>>>(H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4, nullptr, 0, 0);
-    CUDA_CHECK_LAUNCH();
+    if (rowsum) launch_k(k_update_h<true>, dim3(grid), dim3(256), 0, st, H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4, rowsum_partials, d.n_offset, d.refcompat);
+    else        launch_k(k_update_h<false>, dim3(grid), dim3(256), 0, st, H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4, (float*)nullptr, 0ll, 0);
     return rowsum ? grid : 0;
 }
 
 void launch_rowsum_finish2(const float* partials, float* sumH, int nblocks, const Dims& d, cudaStream_t st) {
-    k_rowsum_finish2<<<(d.Kv + 31) / 32, dim3(32, 32), 0, st>>>(partials, sumH, d.Kv, nblocks);
-    CUDA_CHECK_LAUNCH();
+    launch_k(k_rowsum_finish2, dim3((d.Kv + 31) / 32), dim3(32, 32), 0, st, partials, sumH, d.Kv, nblocks);
 }
 
 void launch_gather_rows(const float* src, int ld, int cols, const int* rows, int count, float* dst, cudaStream_t st) {
@@ -381,13 +471,11 @@ void launch_gather_rows(const float* src, int ld, int cols, const int* rows, int
 }
 
 void launch_fold_splits(const float* P, int nsplit, size_t split_stride, float* out, size_t n, cudaStream_t st) {
-    k_fold_splits<<<grid_for(n / 4, 256), 256, 0, st>>>(P, nsplit, split_stride, out, n / 4);
-    CUDA_CHECK_LAUNCH();
+    launch_k(k_fold_splits, dim3(grid_for(n / 4, 256)), dim3(256), 0, st, P, nsplit, split_stride, out, n / 4);
 }
 
 void launch_sum_partials(const double* partials, int n, int nbatch, double* out, cudaStream_t st) {
-    k_sum_partials<<<nbatch, 1024, 0, st>>>(partials, n, out);
-    CUDA_CHECK_LAUNCH();
+    launch_k(k_sum_partials, dim3(nbatch), dim3(1024), 0, st, partials, n, out);
 }
 
 }  // namespace nmf

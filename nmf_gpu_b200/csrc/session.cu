@@ -164,6 +164,7 @@ void session_need_quotient(nmf_session_impl& s) {
 
 // After any change of W or H masters: refresh the TF32 splits the tcgen05 engine reads.
 static void refresh_splits(nmf_session_impl& s, bool w, bool h) {
+    if (w) s.sumW_valid = false;          // every path that rewrites W from outside the iteration comes through here
     if (s.opt.engine != NMF_ENGINE_TCGEN05) return;
     if (w) { launch_split_tf32(s.W, s.Whi, s.Wlo, s.d.szW(), s.stream); }
     if (h) { launch_split_tf32(s.H, s.Hhi, s.Hlo, s.d.szH(), s.stream); }
@@ -370,9 +371,23 @@ static void do_quotient(nmf_session_impl& s, bool with_cost) {
     if (with_cost) { launch_sum_partials(s.cost_partials, s.n_cost_partials, 1, s.cost_dev, s.stream); count_launches(s, 1); }
 }
 
-void iteration_head(nmf_session_impl& s, bool with_cost, PhaseTimer* pt) {
-    // sum cols of W (nmf.cu:134) — first, so the head is exactly "everything that only needs W,H,X"
+// sum cols of W (Matrix::sum_cols, nmf.cu:134) at the head of an iteration.  Small problems (w_update_emits_colsum: a property
+// of the shape, fixed for the session): the W update of the previous iteration left them, and the kernel runs only when W
+// came from somewhere else (upload, generator, a restored restart) — session_run makes that call eagerly before it captures,
+// so a captured iteration never contains it.  Everything else: one k_colsum launch per iteration, as the reference.
+static int nsplit_at_update(const nmf_session_impl& s) {
+    return (s.nranks == 1 && s.opt.engine == NMF_ENGINE_TCGEN05 && s.nsplit > 1) ? s.nsplit : 1;
+}
+static bool w_update_emits_colsum(const nmf_session_impl& s) { return update_w_by_column(s.d, nsplit_at_update(s)); }
+static void ensure_sumw(nmf_session_impl& s, PhaseTimer* pt) {
+    if (w_update_emits_colsum(s) && s.sumW_valid) return;
     PHASE(pt, PH_SUMS, { launch_colsum(s.W, s.sumW, s.d, s.stream); count_launches(s, 1); });
+    s.sumW_valid = true;
+}
+
+void iteration_head(nmf_session_impl& s, bool with_cost, PhaseTimer* pt) {
+    // sum cols of W (nmf.cu:134): the W update of the previous iteration left them (ensure_sumw otherwise)
+    ensure_sumw(s, pt);
     // Z = X ./ max(W*H, EPS)  (nmf.cu:125-131); the KL cost of the current factors rides along
     PHASE(pt, PH_QUOT, do_quotient(s, with_cost));
 }
@@ -388,7 +403,7 @@ static bool fused_check_enabled(const nmf_session_impl& s) {
 static void iteration_head_fused_cost(nmf_session_impl& s, PhaseTimer* pt) {
     const Dims& d = s.d;
     if (!s.Hbak) s.Hbak = dalloc<float>(d.szHa());
-    PHASE(pt, PH_SUMS, { launch_colsum(s.W, s.sumW, d, s.stream); count_launches(s, 1); });
+    ensure_sumw(s, pt);
     PHASE(pt, PH_COST, CUDA_CHECK(cudaMemcpyAsync(s.Hbak, s.H, d.szHa() * 4, cudaMemcpyDeviceToDevice, s.stream)));
     PHASE(pt, PH_GEMM2, {
         const int n = umma::fused_h(s, true); count_launches(s, n);
@@ -415,7 +430,7 @@ void iteration_rest(nmf_session_impl& s, PhaseTimer* pt) {
 // One whole iteration when no cost is wanted: with the fused H step the first quotient never reaches HBM.
 void iteration_full(nmf_session_impl& s, PhaseTimer* pt) {
     if (s.opt.engine == NMF_ENGINE_TCGEN05 && umma::fused_h_enabled(s)) {
-        PHASE(pt, PH_SUMS, { launch_colsum(s.W, s.sumW, s.d, s.stream); count_launches(s, 1); });
+        ensure_sumw(s, pt);
         PHASE(pt, PH_GEMM2, { const int n = umma::fused_h(s); count_launches(s, n); });
         w_half(s, pt);
     } else {
@@ -428,11 +443,16 @@ static void w_half(nmf_session_impl& s, PhaseTimer* pt) {
     const Dims& d = s.d;
     // sum rows of H (nmf.cu:164) into the packed buffer's tail
     // (when the H update ran as its own kernel it left per-block partial sums of the new H: only the fold remains)
-    PHASE(pt, PH_SUMS, {
-        if (s.rowsum_blocks > 0) { launch_rowsum_finish2(s.rowsum_partials, s.sumH, s.rowsum_blocks, d, s.stream); count_launches(s, 1); }
-        else { launch_rowsum(s.H, s.rowsum_partials, s.sumH, d, s.stream); count_launches(s, 2); }
-        s.rowsum_blocks = 0;
-    });
+    // Small single-GPU problems: the W update kernel folds those partial sums itself (one launch fewer).
+    const bool fold_in_update = s.rowsum_blocks > 0 && s.nranks == 1 && w_update_emits_colsum(s);
+    const int rs_blocks = s.rowsum_blocks;
+    if (!fold_in_update) {
+        PHASE(pt, PH_SUMS, {
+            if (s.rowsum_blocks > 0) { launch_rowsum_finish2(s.rowsum_partials, s.sumH, s.rowsum_blocks, d, s.stream); count_launches(s, 1); }
+            else { launch_rowsum(s.H, s.rowsum_partials, s.sumH, d, s.stream); count_launches(s, 2); }
+        });
+    }
+    s.rowsum_blocks = 0;
     const float* P = s.packed; int nsplit = 1; size_t stride = 0;
     if (s.opt.engine == NMF_ENGINE_TCGEN05 && umma::fused_w_enabled(s)) {
         // both of the steps below in one kernel: the quotient goes from TMEM through shared memory into the
@@ -458,8 +478,10 @@ static void w_half(nmf_session_impl& s, PhaseTimer* pt) {
         P = s.packed; nsplit = 1; stride = 0;
     }
     // W = W .* ((Z*H') ./ sumH)   (nmf.cu:172-175)
+    // (small problems: the same kernel leaves the column sums of the new W for the next H step, nmf.cu:134)
     PHASE(pt, PH_UPDW, {
-        launch_update_w(s.W, s.Whi, s.Wlo, P, nsplit, stride, s.sumH, d, s.stream);
+        s.sumW_valid = launch_update_w(s.W, s.Whi, s.Wlo, P, nsplit, stride, s.sumH, d, s.stream,
+                                       fold_in_update ? s.rowsum_partials : nullptr, rs_blocks, s.sumW);
         count_launches(s, 1);
     });
 }
@@ -469,7 +491,7 @@ void session_half_step(nmf_session_impl& s, int which) {
     CUDA_CHECK(cudaSetDevice(s.device));
     if (which == 0) {
         if (s.opt.engine == NMF_ENGINE_TCGEN05 && umma::fused_h_enabled(s)) {
-            launch_colsum(s.W, s.sumW, s.d, s.stream);
+            ensure_sumw(s, nullptr);
             umma::fused_h(s);
         } else {
             iteration_head(s, false, nullptr);
@@ -582,6 +604,8 @@ void session_run(nmf_session_impl& s, float thresh, int max_iter, double t[10], 
     PhaseTimer* pt = pt_own.get();
     const bool graph = s.opt.use_graph && !pt;
     s.rowsum_blocks = 0;
+    struct PdlGuard { explicit PdlGuard(bool on) { set_launch_pdl(on); } ~PdlGuard() { set_launch_pdl(false); } } pdl_guard(s.tune.pdl != 0);
+    if (max_iter > 0 && w_update_emits_colsum(s)) ensure_sumw(s, pt);   // a captured iteration of a small problem never contains the column-sum kernel
     if (graph) build_graphs(s);
 
     EventPair ev;

@@ -28,6 +28,7 @@ struct Tuning {
     int keep_quotient = 0; // NMF_KEEP_QUOTIENT  allocate the M x N quotient buffer even when both half-iterations are fused
     int variant = 0;       // NMF_UMMA_VARIANT   bring-up / timing switches that give WRONG results: honoured only by diagnostic
                            //                    builds (NMF_BUILD_DIAG=1 -> -DNMF_DIAG); a release build ignores the variable
+    int pdl = 1;           // NMF_PDL            programmatic dependent launch between the kernels of an iteration
     int pad64 = 1;         // NMF_PAD_K64        exact semantics: pad K to a multiple of 64 when that lets the half-iterations fuse
 };
 Tuning read_tuning();
@@ -58,6 +59,8 @@ struct nmf_session_impl {
     int fhsplit = 1;                              // the same for the fused H step (shares Hpart)
     float *rowsum_partials = nullptr;
     int rowsum_blocks = 0;                        // > 0: the H update of this iteration left that many partial row sums of the new H
+    bool sumW_valid = false;                      // sumW holds the column sums of the resident W (the W update emits them for the
+                                                  // next iteration; anything else that writes W clears the flag)
     double *cost_partials = nullptr; int n_cost_partials = 0;
     int n_cost_partials_fused = 0;                // partials of the fused H step's cost variant (0: that step is not fused)
     float *Hbak = nullptr;                        // H before a fused H step that carries the cost (allocated on first use)
