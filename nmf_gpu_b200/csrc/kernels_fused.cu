@@ -61,6 +61,29 @@ __device__ __forceinline__ void tmem_ld_32x8(uint32_t taddr, uint32_t (&r)[8]) {
 __device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, uint32_t (&r)[16]) { tmem_ld_32x16(taddr, r); }
 __device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, uint32_t (&r)[8]) { tmem_ld_32x8(taddr, r); }
 
+// registers -> TMEM: 8 / 16 consecutive 32-bit columns of this warp's 32 lanes (the mirror of the loads above)
+__device__ __forceinline__ void tmem_st_cols(uint32_t taddr, const uint32_t (&r)[8]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 :: "r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
+}
+__device__ __forceinline__ void tmem_st_cols(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+                 :: "r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+                    "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]) : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// 256-row MMA over the CTA pair with the A operand in TENSOR MEMORY (each CTA's own 128 rows x 8 tf32 columns at `a_tmem`;
+// K-major by construction) and B in shared memory
+__device__ __forceinline__ void mma_tf32_cg2_ts(uint32_t d_tmem, uint32_t a_tmem, uint32_t blo, uint32_t bhi, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], db, %4, p;\n\t}"
+        :: "r"(d_tmem), "r"(a_tmem), "r"(blo), "r"(bhi), "r"(idesc), "r"(accumulate) : "memory");
+}
+
 // 32-byte global accesses (sm_100: LDG/STG.256): the H-step epilogue moves 128 contiguous bytes per lane row, and a
 // warp instruction touches 32 lines either way, so twice the bytes per instruction halve its trips through the LSU
 __device__ __forceinline__ void ldg256(const float* ptr, float (&r)[8]) {
@@ -72,13 +95,22 @@ __device__ __forceinline__ void stg256(float* ptr, const float (&r)[8]) {
                  :: "l"(ptr), "f"(r[0]), "f"(r[1]), "f"(r[2]), "f"(r[3]), "f"(r[4]), "f"(r[5]), "f"(r[6]), "f"(r[7]) : "memory");
 }
 
-template <bool HSTEP, int NW, bool COST, int BN>
+// YT (K <= 128, where P leaves 128 TMEM columns free): the quotient chunk goes to TENSOR MEMORY instead of shared memory —
+// two 64-column buffers (hi 32 | lo 32) at columns 384..511 — and the second GEMM takes its A operand from there
+// (tcgen05.mma with A in TMEM, the arrangement FlashAttention uses for P*V).  Measured reason (ncu source page of the
+// K = 64 kernels, profiles/r2_ncu_source_c5k64_fused_before.txt): 15-18 % of all warp samples sat on the
+// fence.proxy.async that publishes the workers' shared-memory stores to the tensor core, and the swizzled store
+// addressing is pure issue-slot cost in a loop whose CUDA-core work (~800 issue cycles per chunk and scheduler) already
+// exceeds the chunk's MMA time (768 cycles at K = 64).  A TMEM store needs no proxy fence and no address arithmetic, and
+// the b-stage MMAs stop reading 4 KB of A per dispatch from shared memory.
+template <bool HSTEP, int NW, bool COST, int BN, bool YT>
 __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_constant__ FusedParams p) {
     using FC = FCfg<NW>;
     constexpr int CW = FC::CW;
     constexpr int NCH = BN / 32;                       // 32-column chunks per S tile
     constexpr int SBUF = (BN == F_BN_DB) ? 2 : 1;      // S tiles in TMEM
     static_assert(SBUF * BN == F_BN, "S occupies TMEM columns 0..255, P starts at 256");
+    constexpr uint32_t F_YT_COL = 384, F_YT_BUF = 64;  // YT: quotient buffers in TMEM (P then holds <= 128 columns: 256..383)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* xbuf = smem + F_STAGES * F_STAGE_BYTES;                          // [2] X chunks
@@ -308,6 +340,17 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                 const uint32_t aH = aLo_b + so, aL = aH + (A_TILE_BYTES >> 4), bH = bLo_b + so, bL = bH + (F_B_TILE >> 4);
                 const bool last = (++in_period == p.period) || (c == nch - 1);
                 if (elect_one()) {
+                    if (YT) {
+                        // A = the quotient chunk in tensor memory (buffer yctr & 1: hi at +0, lo at +32; 8 columns per K = 8 step)
+                        const uint32_t yH = tmem_base + F_YT_COL + (yctr & 1u) * F_YT_BUF, yL = yH + 32u;
+                        const uint32_t acc0 = in_period == 1 ? 0u : 1u;
+                        #pragma unroll
+                        for (int ks = 0; ks < BK / UK; ++ks) mma_tf32_cg2_ts(tmem_P, yL + ks * UK, bH + ks * sBb, bHiW_b, idesc_b, ks == 0 ? acc0 : 1u);
+                        #pragma unroll
+                        for (int ks = 0; ks < BK / UK; ++ks) mma_tf32_cg2_ts(tmem_P, yH + ks * UK, bL + ks * sBb, bHiW_b, idesc_b, 1u);
+                        #pragma unroll
+                        for (int ks = 0; ks < BK / UK; ++ks) mma_tf32_cg2_ts(tmem_P, yH + ks * UK, bH + ks * sBb, bHiW_b, idesc_b, 1u);
+                    } else
                     block(tmem_P, aH, aL, bH, bL, aHiW_b, bHiW_b, sAb, sBb, idesc_b, in_period == 1 ? 0u : 1u);
                     mma_commit_cg2_a(empty_of(stage, use), (uint16_t)3);
                     if (last) mma_commit_cg2_a(pfull_a, (uint16_t)3);
@@ -338,6 +381,10 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
         const uint32_t sw = row & 7u;                                         // 16-byte chunk index XOR (row mod 8)
         const uint32_t laneS0 = tmem_S + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * CW);
         const uint32_t laneP = tmem_P + ((uint32_t)(q * 32) << 16);
+        const uint32_t laneY = tmem_base + F_YT_COL + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * CW);   // YT: this warp's columns of a buffer
+        // YT: the `empty` barrier (address, parity) on which the MMAs of the last two b-stages are committed — the quotient
+        // buffer yctr & 1 is free again once the b-stage that read it two chunks ago has retired
+        uint32_t yrel_a0 = 0u, yrel_a1 = 0u, yrel_p0 = 0u, yrel_p1 = 0u;     // (scalars: a dynamically indexed array would live in local memory)
         // this thread's X elements of a chunk.  W step: [column][lane row], no swizzle: 16 scalars 512 B apart.
         // H step: [lane row][32 columns] with the 128-byte swizzle: four 16-byte pieces of its own 128-byte row.
         const uint32_t xoff = HSTEP ? xbuf_a + row * 128u
@@ -457,6 +504,24 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                             }
                         }
                     }
+                    if (YT) {
+                        uint32_t zh[CW], zl[CW];
+                        #pragma unroll
+                        for (int jj = 0; jj < CW; ++jj) {
+                            float hv, lv;
+                            tf32_split_fast(z[jj], hv, lv);
+                            zh[jj] = __float_as_uint(hv); zl[jj] = __float_as_uint(lv);
+                        }
+                        // buffer yctr & 1 was read by the b-stage two chunks ago: wait until those MMAs have retired
+                        const uint32_t yb = yctr & 1u;
+                        if (yctr >= 2u) { mbar_wait_a(yb ? yrel_a1 : yrel_a0, yb ? yrel_p1 : yrel_p0, p.err, 19); tc_fence_after(); }
+                        const uint32_t ra = empty_of(stage, use), rp = (use >> 2) & 1u;      // where THIS chunk's MMAs will be committed
+                        if (yb) { yrel_a1 = ra; yrel_p1 = rp; } else { yrel_a0 = ra; yrel_p0 = rp; }
+                        tmem_st_cols(laneY + yb * F_YT_BUF, zh);
+                        tmem_st_cols(laneY + yb * F_YT_BUF + 32u, zl);
+                        tmem_st_wait();
+                        tc_fence_before();
+                    } else {
                     // the ring slot of this b-stage must have been released by the MMAs that last read it
                     { uint32_t par; const uint32_t eb = empty_prev(stage, use, par); mbar_wait_a(eb, par, p.err, 19); }
                     const uint32_t hi_base = sb + stage * (uint32_t)F_STAGE_BYTES + row_off;
@@ -470,6 +535,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                         sts128(a + (uint32_t)A_TILE_BYTES, lv);
                     }
                     fence_proxy_async_smem();
+                    }
                     __syncwarp();
                     if (elect_one()) {
                         mbar_arrive_cluster(yfull_r + ((yctr & (uint32_t)(F_YRING - 1)) << 3));
@@ -591,13 +657,13 @@ int num_sms_f() {
     return n;
 }
 
-template <bool HSTEP, int NW, bool COST, int BN>
+template <bool HSTEP, int NW, bool COST, int BN, bool YT>
 void launch_fused_nw(const FusedParams& p, cudaStream_t st) {
     // function attributes are per device: one host thread per GPU may launch the same instantiation
     static std::atomic<unsigned long long> configured{0};            // bit d: done on device d
     int dev = 0; CUDA_CHECK(cudaGetDevice(&dev));
     if (!(configured.load(std::memory_order_acquire) >> (dev & 63) & 1ull)) {
-        CUDA_CHECK(cudaFuncSetAttribute(k_fused<HSTEP, NW, COST, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_BYTES));
+        CUDA_CHECK(cudaFuncSetAttribute(k_fused<HSTEP, NW, COST, BN, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_BYTES));
         configured.fetch_or(1ull << (dev & 63), std::memory_order_release);
     }
     cudaLaunchConfig_t cfg{};
@@ -618,22 +684,27 @@ void launch_fused_nw(const FusedParams& p, cudaStream_t st) {
         const int sms = num_sms_f();
         cfg.gridDim = dim3(2u * (unsigned)(sms / 2), 1, 1);
         int n = 0;
-        CUDA_CHECK(cudaOccupancyMaxActiveClusters(&n, k_fused<HSTEP, NW, COST, BN>, &cfg));
+        CUDA_CHECK(cudaOccupancyMaxActiveClusters(&n, k_fused<HSTEP, NW, COST, BN, YT>, &cfg));
         NMF_CHECK(n > 0, "no CTA pair of the fused half-iteration kernel fits on this device");
         max_pairs.store(std::min(n, sms / 2));
     }
     const long long items = (long long)p.tiles_l * p.nsplit * p.nbatch;
     cfg.gridDim = dim3(2u * (unsigned)std::min<long long>(items, max_pairs.load()), 1, 1);
-    CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_fused<HSTEP, NW, COST, BN>, p));
+    CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_fused<HSTEP, NW, COST, BN, YT>, p));
     CUDA_CHECK_LAUNCH();
 }
 
 template <bool HSTEP, bool COST>
 void launch_fused_t(const FusedParams& p, cudaStream_t st) {
+    // the quotient in tensor memory (ytmem) is instantiated for the K <= 128 default (4 worker warps per quadrant) only
     if (p.nw == 4) {
-        if (p.bn == F_BN_DB) launch_fused_nw<HSTEP, 4, COST, F_BN_DB>(p, st); else launch_fused_nw<HSTEP, 4, COST, F_BN>(p, st);
+        if (p.ytmem) {
+            if (p.bn == F_BN_DB) launch_fused_nw<HSTEP, 4, COST, F_BN_DB, true>(p, st); else launch_fused_nw<HSTEP, 4, COST, F_BN, true>(p, st);
+        } else {
+            if (p.bn == F_BN_DB) launch_fused_nw<HSTEP, 4, COST, F_BN_DB, false>(p, st); else launch_fused_nw<HSTEP, 4, COST, F_BN, false>(p, st);
+        }
     } else {
-        if (p.bn == F_BN_DB) launch_fused_nw<HSTEP, 2, COST, F_BN_DB>(p, st); else launch_fused_nw<HSTEP, 2, COST, F_BN>(p, st);
+        if (p.bn == F_BN_DB) launch_fused_nw<HSTEP, 2, COST, F_BN_DB, false>(p, st); else launch_fused_nw<HSTEP, 2, COST, F_BN, false>(p, st);
     }
 }
 
@@ -642,6 +713,7 @@ void launch_fused_t(const FusedParams& p, cudaStream_t st) {
 void launch_fused(bool hstep, bool cost, const FusedParams& p, cudaStream_t st) {
     NMF_CHECK(p.nw == 2 || (p.nw == 4 && p.Kv <= 128), "fused kernel: 4 worker warps per quadrant need a P tile of <= 128 columns");
     NMF_CHECK(!cost || hstep, "fused kernel: only the H step carries the cost");
+    NMF_CHECK(!p.ytmem || (p.nw == 4 && p.Kv <= 128), "fused kernel: the quotient fits in tensor memory only beside a P tile of <= 128 columns");
     if (hstep) { if (cost) launch_fused_t<true, true>(p, st); else launch_fused_t<true, false>(p, st); }
     else launch_fused_t<false, false>(p, st);
 }

@@ -23,6 +23,7 @@ struct Tuning {
     int fhsplit = 0;       // NMF_UMMA_FHSPLIT   forced row-split count of the fused H step (0: the cost model chooses)
     int fuse_nw = 0;       // NMF_UMMA_FUSE_NW   worker warps per TMEM quadrant of the fused kernels (0: 4 when Kv <= 128, else 2)
     int fh_defer = 0;      // NMF_UMMA_FH_DEFER  fused H step leaves the update to k_update_h even without a row split
+    int fuse_yt = 1;       // NMF_UMMA_FUSE_YT   K <= 128: stage the quotient in tensor memory (0: in shared memory, as K > 128 does)
     int fuse_bn = 128;     // NMF_UMMA_FUSE_BN   S tile width of the fused kernels (128 double-buffered, or 256)
     int hsplit = 0;        // NMF_UMMA_HSPLIT    forced row-split count of the two-kernel H update (0: automatic)
     int keep_quotient = 0; // NMF_KEEP_QUOTIENT  allocate the M x N quotient buffer even when both half-iterations are fused

@@ -56,6 +56,7 @@ struct alignas(64) FusedParams {
     double* cost_partials; int Llog, Clog;
     int bn;                          // S tile width the launch runs with (256, or 128 double-buffered)
     int nw;                          // worker warps per TMEM lane quadrant (2 or 4)
+    int ytmem;                       // the quotient chunk is staged in tensor memory (A operand of the second GEMM from TMEM); nw == 4 only
     int defer;                       // H step: store W'*Y sums to P even when nsplit == 1, k_update_h applies the update
     unsigned int* err;
 };

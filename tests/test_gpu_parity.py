@@ -187,6 +187,26 @@ def test_fused_kernel_variants(api, oracle, nw, bn, shape, monkeypatch):
     assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
 
 
+@pytest.mark.parametrize("yt", ["1", "0"])
+@pytest.mark.parametrize("shape", [(700, 1500, 128), (513, 3000, 40), (2100, 900, 64), (300, 5000, 96)])
+def test_fused_quotient_staging(api, oracle, yt, shape, monkeypatch):
+    """K <= 128: the quotient chunk is handed to the second GEMM through TENSOR MEMORY (tcgen05.mma with its A operand in
+    TMEM; NMF_UMMA_FUSE_YT=1, the default) or through shared memory (=0, what K > 128 always does).  Half-steps and 30
+    whole iterations with a cost check, ragged tiles, several work items per CTA pair."""
+    monkeypatch.setenv("NMF_UMMA_FUSE_YT", yt)
+    W, H, X = rand_problem(*shape, seed=13)
+    H1 = api.dbg_h_step(W, H, X, api.options())
+    assert max_rel(H1, oracle.h_step(W, H, X, "exact", acc64=True)) < 2e-5
+    W1 = api.dbg_w_step(W, H, X, api.options())
+    assert max_rel(W1, oracle.w_step(W, H, X, "exact", acc64=True)) < 2e-5
+    Wo, Ho, _, cost = oracle.update_div(W, H, X, 0.0, 30, "exact", acc64=True)
+    Wd, Hd = W.copy(order="F"), H.copy(order="F")
+    res = api.update_div(Wd, Hd, X, 1e-12, 30)
+    assert res.iterations == 30
+    assert max_rel(Wd, Wo) < 1e-4 and max_rel(Hd, Ho) < 1e-4
+    assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
+
+
 @pytest.mark.parametrize("env", [{"NMF_UMMA_FH_DEFER": "1"}, {"NMF_UMMA_FHSPLIT": "1"}, {"NMF_UMMA_FHSPLIT": "3"},
                                  {"NMF_UMMA_FHSPLIT": "64"}])
 def test_fused_h_step_split_switches(api, oracle, env, monkeypatch):
