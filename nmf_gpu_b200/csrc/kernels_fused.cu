@@ -95,9 +95,12 @@ __device__ __forceinline__ void stg256(float* ptr, const float (&r)[8]) {
                  :: "l"(ptr), "f"(r[0]), "f"(r[1]), "f"(r[2]), "f"(r[3]), "f"(r[4]), "f"(r[5]), "f"(r[6]), "f"(r[7]) : "memory");
 }
 
-// YT (K <= 128, where P leaves 128 TMEM columns free): the quotient chunk goes to TENSOR MEMORY instead of shared memory —
-// two 64-column buffers (hi 32 | lo 32) at columns 384..511 — and the second GEMM takes its A operand from there
-// (tcgen05.mma with A in TMEM, the arrangement FlashAttention uses for P*V).  Measured reason (ncu source page of the
+// YT (K <= 128, where P leaves 128 TMEM columns free): the quotient chunk goes to TENSOR MEMORY instead of shared memory
+// and the second GEMM takes its A operand from there (tcgen05.mma with A in TMEM, the arrangement FlashAttention uses
+// for P*V).  The hi half OVERWRITES the S chunk it was computed from (each worker warp reads and rewrites its own lanes
+// and columns; the tensor pipe runs the MMAs of one issuer in order, so the a-stages that later reuse the S buffer cannot
+// overtake the b-stages that read it), the lo half goes to a ring of four 32-column slots at columns 384..511, released
+// by the b-stage's own commit (`yempty`): the hand-off is four chunks deep instead of the three ring slots.  Measured reason (ncu source page of the
 // K = 64 kernels, profiles/r2_ncu_source_c5k64_fused_before.txt): 15-18 % of all warp samples sat on the
 // fence.proxy.async that publishes the workers' shared-memory stores to the tensor core, and the swizzled store
 // addressing is pure issue-slot cost in a loop whose CUDA-core work (~800 issue cycles per chunk and scheduler) already
@@ -110,7 +113,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
     constexpr int NCH = BN / 32;                       // 32-column chunks per S tile
     constexpr int SBUF = (BN == F_BN_DB) ? 2 : 1;      // S tiles in TMEM
     static_assert(SBUF * BN == F_BN, "S occupies TMEM columns 0..255, P starts at 256");
-    constexpr uint32_t F_YT_COL = 384, F_YT_BUF = 64;  // YT: quotient buffers in TMEM (P then holds <= 128 columns: 256..383)
+    constexpr uint32_t F_YT_COL = 384, F_YT_SLOTS = 4; // YT: ring of lo slots in TMEM (P then holds <= 128 columns: 256..383)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* xbuf = smem + F_STAGES * F_STAGE_BYTES;                          // [2] X chunks
@@ -129,7 +132,8 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
     // per slot could be two phases away from the use they wait for (behind: a false "free"; ahead: a wait that never
     // ends).  With four, that takes a drift of 24 ring positions; the roles are never more than KB + 6 <= 14 apart.
     uint64_t* empty = bars + 20;
-    uint32_t* tmem_slot = (uint32_t*)(bars + 20 + F_STAGES * F_EMPTY_WAYS);
+    uint64_t* yempty = bars + 20 + F_STAGES * F_EMPTY_WAYS;      // [4]  YT: MMA -> workers: lo slot read (multicast)
+    uint32_t* tmem_slot = (uint32_t*)(bars + 24 + F_STAGES * F_EMPTY_WAYS);
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
     const int lane = threadIdx.x & 31;
@@ -149,6 +153,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
         for (int s = 0; s < F_YRING; ++s) mbar_init(&yfull[s], 2 * FC::NARR);   // the worker warps of both CTAs
         for (int s = 0; s < 2; ++s) { mbar_init(&sfull[s], 1); mbar_init(&sempty[s], 2 * FC::NARR); }
         mbar_init(pfull, 1); mbar_init(pempty, 2 * FC::NARR);
+        for (int s = 0; s < 4; ++s) mbar_init(&yempty[s], 1);
         fence_barrier_init();
     }
     if (warp == 1) { tmem_alloc_cg2(tmem_slot, TMEM_COLS); tmem_relinquish_cg2(); }
@@ -165,7 +170,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
     const uint32_t bar_a = xbuf_a + (uint32_t)(F_XBUFS * F_XBUF_BYTES);
     const uint32_t full_a = bar_a, yfull_a = bar_a + 4 * 8, sfull_a = bar_a + 8 * 8, sempty_a = bar_a + 10 * 8,
                    pfull_a = bar_a + 12 * 8, pempty_a = bar_a + 13 * 8, xfull_a = bar_a + 14 * 8, xempty_a = bar_a + 16 * 8,
-                   empty_a = bar_a + 20 * 8;
+                   empty_a = bar_a + 20 * 8, yempty_a = bar_a + (20 + F_STAGES * F_EMPTY_WAYS) * 8;
     // ring position = (stage, use): use counts the slot's uses.  Use u of a slot is released on empty[stage][u % 4];
     // whoever fills the slot for use u first waits for use u - 1 (u = 0: a fresh barrier's "preceding phase", passes)
     auto empty_prev = [&](uint32_t stage, uint32_t use, uint32_t& par) {
@@ -309,7 +314,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
             for (int ks = 0; ks < BK / UK; ++ks) mma_tf32_cg2_w(d, aH + ks * sa, aW, bH + ks * sb, bW, idesc, 1u);
         };
         uint32_t stage = 0, use = 0;
-        uint32_t ga = 0, pctr = 0, yctr = 0;
+        uint32_t ga = 0, gb = 0, pctr = 0, yctr = 0;
         auto issue_a = [&]() {                                   // S tile ga (TMEM columns (ga % SBUF) * BN ..) = sum over the k blocks
             const uint32_t b = ga % (uint32_t)SBUF;
             mbar_wait_a(sempty_a + b * 8, ((ga / (uint32_t)SBUF) & 1u) ^ 1u, p.err, 12);   // the tile that last used this S buffer has been read
@@ -341,8 +346,9 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                 const bool last = (++in_period == p.period) || (c == nch - 1);
                 if (elect_one()) {
                     if (YT) {
-                        // A = the quotient chunk in tensor memory (buffer yctr & 1: hi at +0, lo at +32; 8 columns per K = 8 step)
-                        const uint32_t yH = tmem_base + F_YT_COL + (yctr & 1u) * F_YT_BUF, yL = yH + 32u;
+                        // A = the quotient chunk in tensor memory: hi where the S chunk was, lo in ring slot yctr & 3 (8 columns per K = 8 step)
+                        const uint32_t yH = tmem_S + (gb % (uint32_t)SBUF) * (uint32_t)BN + (uint32_t)(c * 32);
+                        const uint32_t yL = tmem_base + F_YT_COL + (yctr & (F_YT_SLOTS - 1u)) * 32u;
                         const uint32_t acc0 = in_period == 1 ? 0u : 1u;
                         #pragma unroll
                         for (int ks = 0; ks < BK / UK; ++ks) mma_tf32_cg2_ts(tmem_P, yL + ks * UK, bH + ks * sBb, bHiW_b, idesc_b, ks == 0 ? acc0 : 1u);
@@ -353,6 +359,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                     } else
                     block(tmem_P, aH, aL, bH, bL, aHiW_b, bHiW_b, sAb, sBb, idesc_b, in_period == 1 ? 0u : 1u);
                     mma_commit_cg2_a(empty_of(stage, use), (uint16_t)3);
+                    if (YT) mma_commit_cg2_a(yempty_a + (yctr & (F_YT_SLOTS - 1u)) * 8, (uint16_t)3);
                     if (last) mma_commit_cg2_a(pfull_a, (uint16_t)3);
                 }
                 __syncwarp();
@@ -360,6 +367,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                 ++yctr;
                 if (++stage == (uint32_t)F_STAGES) { stage = 0; ++use; }
             }
+            ++gb;
         };
         Cur cur, nxt; cur_init(cur); nxt = cur;
         if (SBUF == 2 && cur_valid(nxt)) { issue_a(); cur_next(nxt); }
@@ -381,10 +389,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
         const uint32_t sw = row & 7u;                                         // 16-byte chunk index XOR (row mod 8)
         const uint32_t laneS0 = tmem_S + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * CW);
         const uint32_t laneP = tmem_P + ((uint32_t)(q * 32) << 16);
-        const uint32_t laneY = tmem_base + F_YT_COL + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * CW);   // YT: this warp's columns of a buffer
-        // YT: the `empty` barrier (address, parity) on which the MMAs of the last two b-stages are committed — the quotient
-        // buffer yctr & 1 is free again once the b-stage that read it two chunks ago has retired
-        uint32_t yrel_a0 = 0u, yrel_a1 = 0u, yrel_p0 = 0u, yrel_p1 = 0u;     // (scalars: a dynamically indexed array would live in local memory)
+        const uint32_t laneY = tmem_base + F_YT_COL + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * CW);   // YT: this warp's columns of a lo slot
         // this thread's X elements of a chunk.  W step: [column][lane row], no swizzle: 16 scalars 512 B apart.
         // H step: [lane row][32 columns] with the 128-byte swizzle: four 16-byte pieces of its own 128-byte row.
         const uint32_t xoff = HSTEP ? xbuf_a + row * 128u
@@ -512,13 +517,13 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                             tf32_split_fast(z[jj], hv, lv);
                             zh[jj] = __float_as_uint(hv); zl[jj] = __float_as_uint(lv);
                         }
-                        // buffer yctr & 1 was read by the b-stage two chunks ago: wait until those MMAs have retired
-                        const uint32_t yb = yctr & 1u;
-                        if (yctr >= 2u) { mbar_wait_a(yb ? yrel_a1 : yrel_a0, yb ? yrel_p1 : yrel_p0, p.err, 19); tc_fence_after(); }
-                        const uint32_t ra = empty_of(stage, use), rp = (use >> 2) & 1u;      // where THIS chunk's MMAs will be committed
-                        if (yb) { yrel_a1 = ra; yrel_p1 = rp; } else { yrel_a0 = ra; yrel_p0 = rp; }
-                        tmem_st_cols(laneY + yb * F_YT_BUF, zh);
-                        tmem_st_cols(laneY + yb * F_YT_BUF + 32u, zl);
+                        // hi: in place, over the S values this thread has just read (nobody else touches these lanes and columns)
+                        tmem_st_cols(laneS + (uint32_t)(c * 32), zh);
+                        // lo: ring slot yctr & 3, free once the b-stage that read it four chunks ago has retired (first round: passes)
+                        const uint32_t ys = yctr & (F_YT_SLOTS - 1u);
+                        mbar_wait_a(yempty_a + ys * 8, ((yctr >> 2) & 1u) ^ 1u, p.err, 19);
+                        tc_fence_after();
+                        tmem_st_cols(laneY + ys * 32u, zl);
                         tmem_st_wait();
                         tc_fence_before();
                     } else {

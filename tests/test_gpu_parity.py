@@ -187,6 +187,26 @@ def test_fused_kernel_variants(api, oracle, nw, bn, shape, monkeypatch):
     assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
 
 
+@pytest.mark.parametrize("fuse", ["0", "1"])
+@pytest.mark.parametrize("xs,ws", [(1e-30, 1.0), (1e-20, 1e12), (1e25, 1e-6), (1.0, 1e-18)])
+def test_quotient_extreme_scales(api, oracle, fuse, xs, ws, monkeypatch):
+    """tiny and huge x / y ratios (quotients around 1e-30, 1e-32, 1e31 and 1e18; products W*H down to the EPS clamp):
+    the fused kernels' quotient is reciprocal + one residual correction with a range check per 8 / 16 elements that sends
+    huge or non-finite cases to the IEEE divide; the two-kernel path adds a Newton step and a lower-bound check.  Both
+    must track the oracle's x / max(y, EPS) wherever the result is a normal number."""
+    monkeypatch.setenv("NMF_UMMA_FUSE", fuse)
+    M, N, K = 300, 700, 64
+    W, H, X = rand_problem(M, N, K, seed=77)
+    X = np.asfortranarray((X * np.float32(xs)).astype(np.float32))
+    W = np.asfortranarray((W * np.float32(ws)).astype(np.float32))
+    H1 = api.dbg_h_step(W, H, X, api.options())
+    Hr = oracle.h_step(W, H, X, "exact", acc64=True)
+    assert np.isfinite(H1).all() and max_rel(H1, Hr) < 2e-5
+    W1 = api.dbg_w_step(W, H, X, api.options())
+    Wr = oracle.w_step(W, H, X, "exact", acc64=True)
+    assert np.isfinite(W1).all() and max_rel(W1, Wr) < 2e-5
+
+
 @pytest.mark.parametrize("yt", ["1", "0"])
 @pytest.mark.parametrize("shape", [(700, 1500, 128), (513, 3000, 40), (2100, 900, 64), (300, 5000, 96)])
 def test_fused_quotient_staging(api, oracle, yt, shape, monkeypatch):
