@@ -113,6 +113,25 @@ def host_threads():
         return os.cpu_count() or 1
 
 
+def bind_near_gpu(index):
+    """Run this process (and first-touch its pinned host buffers) on the CPUs next to GPU `index` (NVML's ideal affinity):
+    torchrun does not place its workers, and a shard uploaded from the far socket crosses the inter-socket link
+    (round 1: 11 GB/s per rank at N = 4).  Returns the previous affinity (restored before the CPU baseline runs)."""
+    try:
+        import pynvml
+        prev = os.sched_getaffinity(0)
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1} & prev
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return prev, sorted(cpus)
+    except Exception:
+        return None, None
+
+
 def cpu_baseline(M, N, K, seed, target_s=12.0):
     """The oracle (C++/OpenMP port of the iteration; the reference has no CPU path) on this box's
     host cores, on a bounded column sample of the same workload, scaled to whole-workload iterations/s.
@@ -241,6 +260,8 @@ def main():
         return run_reference_arm(args, M, N, K, seed, desc, rank, world)
     args.warmup = max(args.warmup, 3)
 
+    vis = [v for v in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if v]
+    prev_affinity, near_cpus = bind_near_gpu(int(vis[local]) if local < len(vis) and vis[local].isdigit() else local)
     import torch
     import nmf_gpu_b200.api as api
     torch.cuda.set_device(local)
@@ -392,7 +413,9 @@ def main():
         e2e = {"value": R * args.steps / dt, "unit": "iterations/s",
                "h2d_bytes_per_step": int(4 * (M * n_loc + R * (M * K + K * n_loc)) / args.steps),
                "d2h_bytes_per_step": int(4 * R * (M * K + K * n_loc) / args.steps),
-               "seconds": dt, "call": call, "loop_device_ms": loop_ms}
+               "seconds": dt, "call": call, "loop_device_ms": loop_ms,
+               "outside_loop_seconds": (dt - loop_ms * 1e-3) if loop_ms else None,      # allocation + H2D + D2H (+ graph capture)
+               "host_cpus_near_gpu": len(near_cpus) if near_cpus else None}
         del Xh, Whs, Hhs
     parity = None
     if world > 1:
@@ -417,6 +440,8 @@ def main():
         if world == 1 and R == 1 and not args.no_refcuda:
             line["reference_cuda"] = reference_cuda(M, N, K, args.steps, args.warmup, local)
         if world == 1 and not args.no_cpu:
+            if prev_affinity:
+                os.sched_setaffinity(0, prev_affinity)         # the CPU baseline gets every host core
             line["cpu_baseline"] = cpu_baseline(M, N, K, seed)
         print(json.dumps(line), flush=True)
     if dist is not None:

@@ -437,14 +437,7 @@ int nmf_dbg_quotient(const float* W, const float* H, const float* X, float* Y, d
 int nmf_dbg_h_step(const float* W, float* H, const float* X, int M, int N, int K, const nmf_options* opt) {
     return guarded([&] {
         with_session(W, H, X, M, N, K, opt, [&](nmf_session_impl& s) {
-            if (s.opt.engine == NMF_ENGINE_TCGEN05 && umma::fused_h_enabled(s)) {
-                launch_colsum(s.W, s.sumW, s.d, s.stream);
-                umma::fused_h(s);
-            } else {
-                iteration_head(s, false, nullptr);
-                if (s.opt.engine == NMF_ENGINE_SIMT) simt_update_h(s.W, s.Y, s.sumW, s.H, s.d, s.stream);
-                else umma::update_h(s);
-            }
+            session_half_step(s, 0);              // exactly the H half of an iteration (column sums, quotient, W'Y, update)
             session_download(s, nullptr, H);
         });
     });
@@ -453,18 +446,7 @@ int nmf_dbg_h_step(const float* W, float* H, const float* X, int M, int N, int K
 int nmf_dbg_w_step(float* W, const float* H, const float* X, int M, int N, int K, const nmf_options* opt) {
     return guarded([&] {
         with_session(W, H, X, M, N, K, opt, [&](nmf_session_impl& s) {
-            // the W half of iteration_rest, starting from the given H
-            launch_rowsum(s.H, s.rowsum_partials, s.sumH, s.d, s.stream);
-            const float* P = s.packed; int nsplit = 1; size_t stride = 0;
-            if (s.opt.engine == NMF_ENGINE_SIMT) {
-                simt_quotient(s.W, s.H, s.X, s.Y, nullptr, s.d, s.stream);
-                simt_numer(s.Y, s.H, s.packed, s.d, s.stream);
-            } else {
-                if (umma::fused_w_enabled(s)) umma::fused_w(s);
-                else { umma::quotient(s, false); umma::numer(s); }
-                if (s.nsplit > 1) { P = s.Psplit; nsplit = s.nsplit; stride = s.d.szW(); }
-            }
-            launch_update_w(s.W, s.Whi, s.Wlo, P, nsplit, stride, s.sumH, s.d, s.stream);
+            session_half_step(s, 1);              // exactly the W half of an iteration, starting from the given H
             session_download(s, W, nullptr);
         });
     });

@@ -139,6 +139,16 @@ bool launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nspli
 // whether launch_update_w will run the one-block-per-column kernel for this shape (the caller may then skip the row-sum finish)
 bool update_w_by_column(const Dims& d, int nsplit);
 
+// W step for the `t` (1..4) rows beyond the last whole 256-row block (row0 = 256*floor(M/256); spectrogram heights are
+// 2^k + 1 = 513, 1025, 2049: one row would cost the fused kernel a whole 256-row work item per column split, 11 % of the
+// W step at 2049 rows, 33 % at 513).  On the CUDA cores, plain fp32, IEEE divide:
+//   P[m,k] = sum_n ( X[m,n] / max( sum_k' W[m,k'] H[k',n], EPS ) ) * H[k,n]      for m = row0 .. row0+t-1
+// per-block partial sums -> `part` (w_tail_blocks(Nv) * Kv float4), folded in a fixed order into the rows of P[split 0]
+// (the other splits' rows are zeroed), so that everything downstream — fold, allreduce, W update — runs unchanged.
+int  w_tail_blocks(int Nv);
+void launch_w_tail(const float* W, const float* H, const float* X, float* part, const Dims& d, int row0, int t,
+                   float* P, int nsplit, size_t split_stride, cudaStream_t st);
+
 // dst[j*count + i] = src[j*ld + rows[i]] for j < cols (rows = device array of `count` row indices): sampled rows of a
 // column-major matrix, for the spot checks of full-size runs
 void launch_gather_rows(const float* src, int ld, int cols, const int* rows, int count, float* dst, cudaStream_t st);

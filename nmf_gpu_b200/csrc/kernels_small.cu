@@ -166,16 +166,6 @@ __global__ void __launch_bounds__(256) k_rowsum_partial(const float* __restrict_
     }
 }
 
-// R2 pass 2: ordered sum over the chunks.
-__global__ void k_rowsum_finish(const float* __restrict__ partials, float* __restrict__ sumH, int Kv, int nchunks) {
-    pdl_sync();
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= Kv) return;
-    float s = 0.0f;
-    for (int c = 0; c < nchunks; ++c) s += partials[(size_t)c * Kv + k];
-    sumH[k] = s;
-}
-
 // W update: one thread per 4 consecutive rows of one column (float4, ld is a multiple of 32).
 __global__ void __launch_bounds__(256) k_update_w(float* __restrict__ W, float* __restrict__ Whi, float* __restrict__ Wlo,
                                                   const float* __restrict__ P, int nsplit, size_t split_stride,
@@ -366,6 +356,91 @@ __global__ void __launch_bounds__(1024) k_sum_partials(const double* __restrict_
     }
 }
 
+// ---- W step of the tail rows (see common.hpp) ------------------------------------------------------------------------
+constexpr int kTailCols = 512;            // columns per block (8 warps x 64 columns)
+// KJ = Kr / 32 values of k per lane.  A warp walks columns; its lanes hold W[tail rows, k] and the running sums for their k.
+template <int KJ>
+__global__ void __launch_bounds__(256) k_w_tail(const float* __restrict__ W, const float* __restrict__ H, const float* __restrict__ X,
+                                                float4* __restrict__ part, int Mv, int ldH, int Kr, int Nv, int row0, int t) {
+    pdl_sync();
+    const int koff = blockIdx.y * Kr;                       // restart
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float w[4][KJ], acc[4][KJ];
+    #pragma unroll
+    for (int i = 0; i < 4; ++i)
+        #pragma unroll
+        for (int j = 0; j < KJ; ++j) {
+            w[i][j] = i < t ? W[(size_t)(koff + lane + 32 * j) * Mv + row0 + i] : 0.0f;
+            acc[i][j] = 0.0f;
+        }
+    const int n0 = blockIdx.x * kTailCols, n1 = min(Nv, n0 + kTailCols);
+    // two columns per trip (n and n + 8): two independent load -> reduce -> divide chains in flight per warp
+    for (int n = n0 + warp; n < n1; n += 16) {
+        const bool two = n + 8 < n1;
+        const int nb = two ? n + 8 : n;
+        float ha[KJ], hb[KJ];
+        const float* hca = H + (size_t)n * ldH + koff + lane;
+        const float* hcb = H + (size_t)nb * ldH + koff + lane;
+        #pragma unroll
+        for (int j = 0; j < KJ; ++j) { ha[j] = hca[32 * j]; hb[j] = hcb[32 * j]; }
+        const float xa = lane < t ? X[(size_t)n * Mv + row0 + lane] : 0.0f;      // lane i holds x of tail row i
+        const float xb = (two && lane < t) ? X[(size_t)nb * Mv + row0 + lane] : 0.0f;   // (0 for a missing second column: adds nothing)
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (i < t) {                                    // uniform
+                float sa = 0.0f, sb = 0.0f;
+                #pragma unroll
+                for (int j = 0; j < KJ; ++j) { sa = fmaf(w[i][j], ha[j], sa); sb = fmaf(w[i][j], hb[j], sb); }
+                sa = warp_sum(sa); sb = warp_sum(sb);       // (W*H)[m,n], every lane
+                const float ya = __shfl_sync(0xffffffffu, xa, i) / clampE(sa);  // set_epsilon + vec_div, nmf.cu:158-161
+                const float yb = __shfl_sync(0xffffffffu, xb, i) / clampE(sb);
+                #pragma unroll
+                for (int j = 0; j < KJ; ++j) acc[i][j] = fmaf(yb, hb[j], fmaf(ya, ha[j], acc[i][j]));
+            }
+        }
+    }
+    // the 8 warps of the block, in order
+    __shared__ float sm[8][4][KJ * 32];
+    #pragma unroll
+    for (int i = 0; i < 4; ++i)
+        #pragma unroll
+        for (int j = 0; j < KJ; ++j) sm[warp][i][lane + 32 * j] = acc[i][j];
+    __syncthreads();
+    for (int k = threadIdx.x; k < Kr; k += 256) {
+        float4 v = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        for (int wv = 0; wv < 8; ++wv) { v.x += sm[wv][0][k]; v.y += sm[wv][1][k]; v.z += sm[wv][2][k]; v.w += sm[wv][3][k]; }
+        part[(size_t)blockIdx.x * ((size_t)gridDim.y * Kr) + koff + k] = v;
+    }
+}
+
+// one block per stacked k: ordered fold of the per-block partial sums (double), then the tail rows of P: split 0 = the sums,
+// every other split = 0 (row0 is a multiple of 4 and ld a multiple of 32: one aligned float4 per column)
+__global__ void __launch_bounds__(256) k_w_tail_fold(const float4* __restrict__ part, int nblocks, int Kv, float* __restrict__ P, int nsplit,
+                                                     size_t split_stride, int Mv, int row0) {
+    pdl_sync();
+    const int k = blockIdx.x;
+    double a[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int b = threadIdx.x; b < nblocks; b += 256) {
+        const float4 v = part[(size_t)b * Kv + k];
+        a[0] += v.x; a[1] += v.y; a[2] += v.z; a[3] += v.w;
+    }
+    __shared__ double red[8][4];
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) a[i] += __shfl_xor_sync(0xffffffffu, a[i], o);
+    }
+    if ((threadIdx.x & 31) == 0) { for (int i = 0; i < 4; ++i) red[threadIdx.x >> 5][i] = a[i]; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s[4] = {0.0, 0.0, 0.0, 0.0};
+        for (int wv = 0; wv < 8; ++wv) for (int i = 0; i < 4; ++i) s[i] += red[wv][i];
+        float* p0 = P + (size_t)k * Mv + row0;
+        *reinterpret_cast<float4*>(p0) = make_float4((float)s[0], (float)s[1], (float)s[2], (float)s[3]);
+        for (int sp = 1; sp < nsplit; ++sp) *reinterpret_cast<float4*>(p0 + (size_t)sp * split_stride) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+}
+
 __global__ void k_gather_rows(const float* __restrict__ src, int ld, int cols, const int* __restrict__ rows, int count,
                               float* __restrict__ dst) {
     const size_t total = (size_t)cols * count;
@@ -431,7 +506,9 @@ void launch_rowsum(const float* H, float* partials, float* sumH, const Dims& d, 
     const int KX = std::min(d.Kv / 4, 64), NY = 256 / KX;
     dim3 grid((d.Kv / 4 + KX - 1) / KX, nch), block(KX, NY);
     launch_k(k_rowsum_partial, grid, block, 0, st, H, partials, d.Kv, d.Nv, d.n_offset, d.refcompat);
-    launch_k(k_rowsum_finish, dim3((d.Kv + 127) / 128), dim3(128), 0, st, (const float*)partials, sumH, d.Kv, nch);
+    // ordered fold of the chunks: 32 groups of chunks in parallel per k (one thread per k walking all chunks was a
+    // chain of ~2000 dependent loads at 10^6 columns: 100+ us, more than the pass over H itself)
+    launch_k(k_rowsum_finish2, dim3((d.Kv + 31) / 32), dim3(32, 32), 0, st, (const float*)partials, sumH, d.Kv, nch);
 }
 
 // the one-block-per-column kernel pays when the launch count matters more than the bytes: up to 64 MB of partials + W
@@ -462,6 +539,22 @@ int launch_update_h(float* H, float* Hhi, float* Hlo, const float* P, int nsplit
 
 void launch_rowsum_finish2(const float* partials, float* sumH, int nblocks, const Dims& d, cudaStream_t st) {
     launch_k(k_rowsum_finish2, dim3((d.Kv + 31) / 32), dim3(32, 32), 0, st, partials, sumH, d.Kv, nblocks);
+}
+
+int w_tail_blocks(int Nv) { return (Nv + kTailCols - 1) / kTailCols; }
+
+void launch_w_tail(const float* W, const float* H, const float* X, float* part, const Dims& d, int row0, int t,
+                   float* P, int nsplit, size_t split_stride, cudaStream_t st) {
+    NMF_CHECK(t >= 1 && t <= 4 && row0 % 4 == 0 && d.Kr % 64 == 0 && d.Kr <= 256, "launch_w_tail: unsupported shape");
+    const dim3 grid(w_tail_blocks(d.Nv), d.R), block(256);
+    float4* part4 = reinterpret_cast<float4*>(part);
+    switch (d.Kr / 32) {
+        case 2: launch_k(k_w_tail<2>, grid, block, 0, st, W, H, X, part4, d.Mv, d.Kv, d.Kr, d.Nv, row0, t); break;
+        case 4: launch_k(k_w_tail<4>, grid, block, 0, st, W, H, X, part4, d.Mv, d.Kv, d.Kr, d.Nv, row0, t); break;
+        case 6: launch_k(k_w_tail<6>, grid, block, 0, st, W, H, X, part4, d.Mv, d.Kv, d.Kr, d.Nv, row0, t); break;
+        default: launch_k(k_w_tail<8>, grid, block, 0, st, W, H, X, part4, d.Mv, d.Kv, d.Kr, d.Nv, row0, t); break;
+    }
+    launch_k(k_w_tail_fold, dim3(d.Kv), dim3(256), 0, st, (const float4*)part4, (int)grid.x, d.Kv, P, nsplit, split_stride, d.Mv, row0);
 }
 
 void launch_gather_rows(const float* src, int ld, int cols, const int* rows, int count, float* dst, cudaStream_t st) {

@@ -74,7 +74,7 @@ nmf_session_impl::~nmf_session_impl() {
     if (g_rest) cudaGraphExecDestroy(g_rest);
     if (plan) umma::plan_destroy(plan);
     if (nccl) nccl_destroy(nccl);
-    float* fl[] = {W, H, X, Y, Whi, Wlo, Hhi, Hlo, sumW, packed, Psplit, Hpart, rowsum_partials, Hbak, Wfin, Hfin};
+    float* fl[] = {W, H, X, Y, Whi, Wlo, Hhi, Hlo, sumW, packed, Psplit, Hpart, rowsum_partials, Hbak, Wfin, Hfin, tail_part};
     for (float* p : fl) if (p) cudaFree(p);
     if (cost_partials) cudaFree(cost_partials);
     if (cost_dev) cudaFree(cost_dev);
@@ -132,7 +132,19 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
             s->Hhi = dalloc<float>(d.szHa()); s->Hlo = dalloc<float>(d.szHa());
             s->n_cost_partials = umma::cost_partial_count(d, tn);
             s->n_cost_partials_fused = umma::fused_cost_partial_count(d, opt.tf32_passes, tn);
-            s->nsplit = umma::numer_splits(d, tn);
+            // W step: the (at most 4) rows beyond the last whole 256-row block leave the fused kernel (common.hpp, launch_w_tail)
+            {
+                const int q = d.M / 256, t = d.M - 256 * q;
+                // measured (profiles/r2_w_tail_ab.txt): pays at C3 (10^6 columns: the fused kernel's wasted row block costs more than
+                // the extra kernel), loses at C2 (20000 columns: two more launches and a latency-bound kernel on 40 blocks):
+                // on from 65536 columns (NMF_W_TAIL=2 forces it, =0 never)
+                const bool pays = tn.w_tail >= 2 || d.Nv >= 65536;
+                if (tn.w_tail != 0 && pays && !d.refcompat && q >= 1 && t >= 1 && t <= 4 && umma::fused_both_wanted(d, opt.tf32_passes, tn)) {
+                    s->tail_t = t; s->tail_row0 = 256 * q;
+                    s->tail_part = dalloc<float>((size_t)w_tail_blocks(d.Nv) * d.Kv * 4);
+                }
+            }
+            s->nsplit = umma::numer_splits(d, tn, s->tail_t ? s->tail_row0 / 256 : 0);
             if (s->nsplit > 1) s->Psplit = dalloc<float>((size_t)s->nsplit * d.szW());
             s->hsplit = umma::updh_splits(d, tn);
             s->fhsplit = umma::fused_h_splits(d, opt.tf32_passes, tn);
@@ -457,7 +469,13 @@ static void w_half(nmf_session_impl& s, PhaseTimer* pt) {
     if (s.opt.engine == NMF_ENGINE_TCGEN05 && umma::fused_w_enabled(s)) {
         // both of the steps below in one kernel: the quotient goes from TMEM through shared memory into the
         // second MMA and never reaches HBM
-        PHASE(pt, PH_GEMM2, { umma::fused_w(s); count_launches(s, 1); });
+        PHASE(pt, PH_GEMM2, {
+            umma::fused_w(s); count_launches(s, 1);
+            if (s.tail_t) {
+                launch_w_tail(s.W, s.H, s.X, s.tail_part, d, s.tail_row0, s.tail_t, s.nsplit > 1 ? s.Psplit : s.packed, s.nsplit, d.szW(), s.stream);
+                count_launches(s, 2);
+            }
+        });
     } else {
         // Z = X ./ max(W*H, EPS) with the new H (nmf.cu:155-161)
         PHASE(pt, PH_QUOT, do_quotient(s, false));

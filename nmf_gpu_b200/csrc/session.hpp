@@ -29,6 +29,8 @@ struct Tuning {
     int keep_quotient = 0; // NMF_KEEP_QUOTIENT  allocate the M x N quotient buffer even when both half-iterations are fused
     int variant = 0;       // NMF_UMMA_VARIANT   bring-up / timing switches that give WRONG results: honoured only by diagnostic
                            //                    builds (NMF_BUILD_DIAG=1 -> -DNMF_DIAG); a release build ignores the variable
+    int w_tail = 1;        // NMF_W_TAIL         W step: rows beyond the last whole 256-row block (at most 4) on the CUDA cores
+                           //                    (1: from 65536 columns, where it pays; 2: always; 0: never)
     int pdl = 1;           // NMF_PDL            programmatic dependent launch between the kernels of an iteration
     int pad64 = 1;         // NMF_PAD_K64        exact semantics: pad K to a multiple of 64 when that lets the half-iterations fuse
 };
@@ -58,6 +60,9 @@ struct nmf_session_impl {
     float *Psplit = nullptr; int nsplit = 1;      // split-N partial numerators (tcgen05 engine)
     float *Hpart = nullptr; int hsplit = 1;       // split-M partial W'*Y of the H update (small problems only)
     int fhsplit = 1;                              // the same for the fused H step (shares Hpart)
+    // W step, tail rows (M = 256 q + t, 1 <= t <= 4, exact semantics): rows 256 q .. are taken out of the fused W kernel
+    // (a whole 256-row work item for one spectrogram bin) and run on the CUDA cores (launch_w_tail); 0: no tail path
+    int tail_t = 0, tail_row0 = 0; float* tail_part = nullptr;
     float *rowsum_partials = nullptr;
     int rowsum_blocks = 0;                        // > 0: the H update of this iteration left that many partial row sums of the new H
     bool sumW_valid = false;                      // sumW holds the column sums of the resident W (the W update emits them for the
@@ -111,7 +116,7 @@ namespace umma {
 Plan* plan_create(nmf_session_impl& s);
 void  plan_destroy(Plan* p);
 int   cost_partial_count(const Dims& d, const Tuning& tn);
-int   numer_splits(const Dims& d, const Tuning& tn);
+int   numer_splits(const Dims& d, const Tuning& tn, int row_blocks = 0);   // row_blocks > 0: that many 256-row blocks instead of all of Mv
 int   updh_splits(const Dims& d, const Tuning& tn);
 void  quotient(nmf_session_impl& s, bool with_cost);
 void  update_h(nmf_session_impl& s);

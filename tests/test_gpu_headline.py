@@ -128,6 +128,28 @@ def test_k_not_multiple_of_64_runs_fused(api, oracle, K):
     assert max_rel(W2, Wo) <= 1e-4 and max_rel(H2, Ho) <= 1e-4
 
 
+@pytest.mark.parametrize("shape", [(513, 3000, 40), (257, 700, 64), (514, 1500, 128), (1027, 900, 192), (516, 2100, 256), (2049, 1300, 128)])
+def test_w_step_tail_rows(api, oracle, shape, monkeypatch):
+    """spectrogram heights 2^k + 1 (C2: 513, C3: 2049): the 1..4 rows beyond the last whole 256-row block are taken out of
+    the fused W kernel (they would cost a whole 256-row work item per column split) and run on the CUDA cores
+    (launch_w_tail; on from 65536 columns, where it pays — NMF_W_TAIL=2 forces it here, =0 keeps the rows in the fused
+    kernel).  Both ways against the oracle, half-step and 30 iterations."""
+    M, N, K = shape
+    W, H, X = rand_problem(M, N, K, seed=M + K)
+    ref = oracle.w_step(W, H, X, "exact", acc64=True)
+    Wo, Ho, _, cost = oracle.update_div(W, H, X, 0.0, 30, "exact", acc64=True)
+    for tail in ("2", "0"):
+        monkeypatch.setenv("NMF_W_TAIL", tail)
+        W1 = api.dbg_w_step(W, H, X, api.options())
+        assert max_rel(W1, ref) < 2e-5, f"NMF_W_TAIL={tail}"
+        assert max_rel(W1[256 * (M // 256):], ref[256 * (M // 256):]) < 2e-5        # the tail rows themselves
+        Wd, Hd = W.copy(order="F"), H.copy(order="F")
+        res = api.update_div(Wd, Hd, X, 1e-12, 30)
+        assert res.iterations == 30
+        assert max_rel(Wd, Wo) <= 1e-4 and max_rel(Hd, Ho) <= 1e-4
+        assert abs(oracle.kl(Wd, Hd, X) - cost) / cost <= 1e-5
+
+
 # ---------------------------------------------------------------------------------------------
 # (d) BASELINE C2 as specified, exact semantics: 513 x 20000, K = 40, seed 1, 200 iterations
 # ---------------------------------------------------------------------------------------------
