@@ -206,6 +206,20 @@ int nmf_dbg_w_step(float *W, const float *H, const float *X, int M, int N, int K
  * (sum_cols/sum_rows + set_epsilon, nmf.cu:134-135,164-165). */
 int nmf_dbg_sums(const float *W, const float *H, float *sumW, float *sumH, int M, int N, int K,
                  const nmf_options *opt);
+/* Row sums of H with NO allocation — no counterpart in the reference; added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The same two kernels as the session's sum_rows replacement (cuda/matrix.cu:379-503 there), but their per-chunk
+ * partial sums live in a device array built into the library (4 MB per GPU that loads it, held until exit) instead of a
+ * session buffer.  The call allocates nothing on host-visible CUDA APIs: no cudaMalloc / cudaFree / session.
+ *   H_dev    : DEVICE pointer, K x N column-major fp32, leading dimension K, 16-byte aligned; K a multiple of 4
+ *   sumH_dev : DEVICE pointer, K floats: sumH[k] = sum_n H[k,n] (not clamped)
+ *   stream   : a cudaStream_t (NULL = the default stream); the call only enqueues, it does not synchronise
+ * Limit: ceil(N/512) * K <= 1 048 576 (e.g. K = 256: N <= 2 097 152); beyond it the call fails with a message
+ * (non-zero return in error mode 1) and launches nothing.  The pointers must belong to the CURRENT device.
+ * Every call on a device shares the one array: calls that overlap on the GPU (different streams, no ordering) race.
+ * Nothing in the array has to start at zero, so back-to-back calls on one stream need no clearing. */
+int nmf_rowsum_noalloc(const float *H_dev, int K, int N, float *sumH_dev, void *stream);
+
 /* Raw tensor-core contraction used by all three GEMMs, for descriptor/layout bring-up:
  * which = 0: C(MxN) = A(MxK)*B(KxN);  1: C(KxN) = A(MxK)'*B(MxN);  2: C(MxK) = A(MxN)*B(KxN)'
  * (shapes named as in the NMF use: A,B,C column-major).  passes = 1 or 3. */

@@ -100,6 +100,7 @@ _SIGNATURES = {
                                       ctypes.POINTER(nmf_options)]),
     "nmf_dbg_sums": (ctypes.c_int, [_f32p, _f32p, _f32p, _f32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                     ctypes.POINTER(nmf_options)]),
+    "nmf_rowsum_noalloc": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]),
     "nmf_dbg_gemm": (ctypes.c_int, [ctypes.c_int, _f32p, _f32p, _f32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                     ctypes.c_int, ctypes.POINTER(nmf_options)]),
 }
@@ -370,6 +371,12 @@ def dbg_sums(W, H, opt=None):
     sw = np.empty(K, dtype=np.float32); sh = np.empty(K, dtype=np.float32)
     _check(lib().nmf_dbg_sums(_p(W), _p(H), _p(sw), _p(sh), M, N, K, _o(opt)))
     return sw, sh
+
+
+def rowsum_noalloc(H_dev_ptr, K, N, sumH_dev_ptr, stream=None):
+    """nmf_rowsum_noalloc on raw DEVICE addresses (ints): row sums of a K x N column-major matrix, nothing allocated"""
+    _check(lib().nmf_rowsum_noalloc(ctypes.c_void_p(H_dev_ptr), int(K), int(N), ctypes.c_void_p(sumH_dev_ptr),
+                                    ctypes.c_void_p(stream) if stream else None))
 
 
 def dbg_gemm(which, A, B, M, N, K, passes=3, opt=None):

@@ -470,6 +470,10 @@ int nmf_dbg_sums(const float* W, const float* H, float* sumW, float* sumH, int M
     });
 }
 
+int nmf_rowsum_noalloc(const float* H_dev, int K, int N, float* sumH_dev, void* stream) {
+    return guarded([&] { rowsum_noalloc(H_dev, K, N, sumH_dev, (cudaStream_t)stream); });
+}
+
 int nmf_dbg_gemm(int which, const float* A, const float* B, float* C, int M, int N, int K, int passes,
                  const nmf_options* opt) {
     return guarded([&] {

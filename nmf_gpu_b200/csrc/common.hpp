@@ -127,6 +127,11 @@ void launch_colsum(const float* W, float* sumW, const Dims& d, cudaStream_t st);
 int  rowsum_partial_count(const Dims& d);
 void launch_rowsum(const float* H, float* partials, float* sumH, const Dims& d, cudaStream_t st);
 
+// sumH_dev[k] = sum_n H_dev[k + n*K] with the partial sums in a built-in device array: no allocation of any kind
+// (nmf_rowsum_noalloc).  Limit: ceil(N/512) * K <= rowsum_noalloc_max_floats().
+size_t rowsum_noalloc_max_floats();
+void rowsum_noalloc(const float* H_dev, int K, int N, float* sumH_dev, cudaStream_t st);
+
 // W[m,k] <- W[m,k] * ((sum_s P[s][m,k]) / max(sumH[k],EPS))   (reference: row_divide + element_multiply,
 // cuda/nmf.cu:172-175).  The divide is skipped when !d.w_divide.  Optionally writes the TF32 split.
 // Small problems (the launch count matters more than the bytes): one block per column k, which can also

@@ -2,6 +2,8 @@
 // the H row sums (R2), the W multiplicative update, ordered partial-sum finishes.
 // All reductions are warp-shuffle trees with a fixed order (no float atomics): run-to-run
 // bit-reproducible, which the 1e-4 @ 100 iterations parity budget needs (SURVEY.md §7 "Determinism").
+#include <mutex>
+
 #include "common.hpp"
 #include "tf32.cuh"
 
@@ -509,6 +511,51 @@ void launch_rowsum(const float* H, float* partials, float* sumH, const Dims& d, 
     // ordered fold of the chunks: 32 groups of chunks in parallel per k (one thread per k walking all chunks was a
     // chain of ~2000 dependent loads at 10^6 columns: 100+ us, more than the pass over H itself)
     launch_k(k_rowsum_finish2, dim3((d.Kv + 31) / 32), dim3(32, 32), 0, st, (const float*)partials, sumH, d.Kv, nch);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Row sums of H without any allocation (nmf_rowsum_noalloc, include/nmf.h): the same two kernels as launch_rowsum, with
+// their per-chunk partial sums in a file-scope device array instead of a session's cudaMalloc'ed buffer — for callers
+// that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid it).  4 MB per GPU that loads the
+// library, held until exit.  Every call on a device shares the array: calls that overlap on the GPU (different streams)
+// race on it.  Nothing in it has to start at zero — pass 1 overwrites every partial that pass 2 reads — so the previous
+// call's contents are harmless.
+// ---------------------------------------------------------------------------------------------
+constexpr size_t kNoAllocScratchFloats = (size_t)1 << 20;
+static __device__ __align__(256) float g_rowsum_scratch[kNoAllocScratchFloats];
+
+size_t rowsum_noalloc_max_floats() { return kNoAllocScratchFloats; }
+
+void rowsum_noalloc(const float* H_dev, int K, int N, float* sumH_dev, cudaStream_t st) {
+    NMF_CHECK(H_dev != nullptr && sumH_dev != nullptr, "nmf_rowsum_noalloc: NULL pointer");
+    NMF_CHECK(K > 0 && N > 0, "nmf_rowsum_noalloc: K and N must be positive");
+    NMF_CHECK(K % 4 == 0 && ((uintptr_t)H_dev & 15) == 0, "nmf_rowsum_noalloc: K must be a multiple of 4 and H 16-byte aligned");
+    const int nch = (N + kRowsumChunk - 1) / kRowsumChunk;
+    NMF_CHECK((size_t)nch * (size_t)K <= kNoAllocScratchFloats && nch <= 65535,
+              "nmf_rowsum_noalloc: ceil(N/512) * K = " + std::to_string((size_t)nch * (size_t)K) + " partial sums exceed the built-in scratch of " +
+              std::to_string(kNoAllocScratchFloats) + " floats (4 MB): use a session, which allocates its own");
+    // In host code `g_rowsum_scratch` is only a stand-in for the symbol, not a device address: resolve it once per device,
+    // with that device current (the caller's current device is the one the pointers belong to)
+    static float* scratch_of[64] = {nullptr};
+    static std::mutex mu;
+    int dev = 0;
+    CUDA_CHECK(cudaGetDevice(&dev));
+    NMF_CHECK(dev >= 0 && dev < 64, "nmf_rowsum_noalloc: device ordinal out of range");
+    float* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!scratch_of[dev]) {
+            float* p = nullptr;
+            CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_rowsum_scratch));
+            NMF_CHECK(p != nullptr, "nmf_rowsum_noalloc: cudaGetSymbolAddress returned NULL");
+            scratch_of[dev] = p;
+        }
+        scratch = scratch_of[dev];
+    }
+    const int KX = std::min(K / 4, 64), NY = 256 / KX;
+    dim3 grid((K / 4 + KX - 1) / KX, nch), block(KX, NY);
+    launch_k(k_rowsum_partial, grid, block, 0, st, H_dev, scratch, K, N, 0ll, 0);
+    launch_k(k_rowsum_finish2, dim3((K + 31) / 32), dim3(32, 32), 0, st, (const float*)scratch, sumH_dev, K, nch);
 }
 
 // the one-block-per-column kernel pays when the launch count matters more than the bytes: up to 64 MB of partials + W
