@@ -25,7 +25,7 @@ def main():
         opt = api.options(semantics=mode)
         os.environ["NMF_NUM_GPUS"] = "1"
         W1 = W.copy(order="F"); H1 = H.copy(order="F")
-        r1 = api.update_div(W1, H1, X, 1e-9, iters, opt=opt)
+        r1 = api.update_div(W1, H1, X, 1e-9, iters, verbose=verbose, opt=opt)   # same verbose: a verbose run closes with one more cost
         os.environ["NMF_NUM_GPUS"] = str(g)
         Wg = W.copy(order="F"); Hg = H.copy(order="F")
         t = np.zeros(10)
