@@ -89,6 +89,7 @@ _SIGNATURES = {
     "nmf_session_share_comm": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
     "nmf_session_fill_planted": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_ulonglong, ctypes.c_int, ctypes.c_float]),
     "nmf_session_fused_steps": (ctypes.c_int, [ctypes.c_void_p]),
+    "nmf_session_corr_bf16": (ctypes.c_int, [ctypes.c_void_p]),
     "nmf_session_run": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_float, ctypes.c_int, _f64p, ctypes.c_int,
                                        ctypes.POINTER(nmf_result)]),
     "nmf_session_cost": (ctypes.c_int, [ctypes.c_void_p, _f64p]),
@@ -303,6 +304,10 @@ class Session:
     def fused_steps(self):
         """bit 0: W step fused, bit 1: H step fused (one kernel per half-iteration, the quotient never in HBM)"""
         return int(lib().nmf_session_fused_steps(self._h))
+
+    def corr_bf16(self):
+        """True when the fused kernels run the correction passes of the 3xTF32 products as BF16 MMAs (K = 256 by default)"""
+        return bool(lib().nmf_session_corr_bf16(self._h))
 
     def fill_planted(self, seed, rank, noise=0.05):
         """X <- planted rank-`rank` product with +-noise multiplicative uniform noise (W, H untouched)"""

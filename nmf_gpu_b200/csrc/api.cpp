@@ -388,6 +388,8 @@ int nmf_session_fused_steps(const nmf_session* s) {
     return (umma::fused_w_enabled(*s) ? 1 : 0) | (umma::fused_h_enabled(*s) ? 2 : 0);
 }
 
+int nmf_session_corr_bf16(const nmf_session* s) { return (s && s->Wbf != nullptr) ? 1 : 0; }
+
 int nmf_nccl_unique_id(void* id128) { return guarded([&] { nccl_unique_id(id128); }); }
 int nmf_session_join(nmf_session* s, int rank, int nranks, const void* id128) {
     return guarded([&] { NMF_CHECK(s, "NULL session"); nccl_join(*s, rank, nranks, id128); });

@@ -115,7 +115,9 @@ void launch_fill_planted(float* x, int rows, int cols, int ld, long long col_off
 void launch_fill_uniform(float* a, int rows, int cols, int ld, long long col_offset,
                          unsigned long long seed, int tag, cudaStream_t st);
 // hi = x with the low 13 mantissa bits cleared (exactly representable in TF32), lo = x - hi (exact).
-void launch_split_tf32(const float* x, float* hi, float* lo, size_t n, cudaStream_t st);
+// bf / lb (both or neither): also the BF16 forms of the correction operands, bf16(x) and bf16(x - hi)
+void launch_split_tf32(const float* x, float* hi, float* lo, size_t n, cudaStream_t st,
+                       unsigned short* bf = nullptr, unsigned short* lb = nullptr);
 
 // sumW[k] = sum_m W[m,k]  (R1; reference: Matrix::sum_cols + reduce2d, cuda/matrix.cu:261-377,642-687)
 // refcompat: only rows m with (m mod 64) in {0,1,2,4,8,16,32} (the reference's stale-read tail).
@@ -140,7 +142,8 @@ void rowsum_noalloc(const float* H_dev, int K, int N, float* sumH_dev, cudaStrea
 // — then neither the row-sum finish nor the column-sum kernel runs.  Returns true when sumW_out was written.
 bool launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nsplit, size_t split_stride,
                      float* sumH, const Dims& d, cudaStream_t st,
-                     const float* rs_partials = nullptr, int rs_blocks = 0, float* sumW_out = nullptr);
+                     const float* rs_partials = nullptr, int rs_blocks = 0, float* sumW_out = nullptr,
+                     unsigned short* Wbf = nullptr, unsigned short* Wlb = nullptr);
 // whether launch_update_w will run the one-block-per-column kernel for this shape (the caller may then skip the row-sum finish)
 bool update_w_by_column(const Dims& d, int nsplit);
 
@@ -164,7 +167,8 @@ void launch_fold_splits(const float* P, int nsplit, size_t split_stride, float* 
 // With `rowsum_partials` (rowsum_partial_count(d) * d.Kv floats) and Kv in {64, 128, 256} the kernel also emits per-block
 // partial row sums of the new H; returns the number of blocks that wrote them (0: none, run launch_rowsum instead).
 int  launch_update_h(float* H, float* Hhi, float* Hlo, const float* P, int nsplit, size_t split_stride,
-                     const float* sumW, const Dims& d, cudaStream_t st, float* rowsum_partials = nullptr);
+                     const float* sumW, const Dims& d, cudaStream_t st, float* rowsum_partials = nullptr,
+                     unsigned short* Hbf = nullptr, unsigned short* Hlb = nullptr);
 // sumH = ordered fold of the `nblocks` partial row sums launch_update_h left in `partials`
 void launch_rowsum_finish2(const float* partials, float* sumH, int nblocks, const Dims& d, cudaStream_t st);
 

@@ -71,7 +71,42 @@ __device__ __forceinline__ void tmem_st_cols(uint32_t taddr, const uint32_t (&r)
                  :: "r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
                     "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]) : "memory");
 }
+__device__ __forceinline__ void tmem_st_x4(uint32_t taddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" :: "r"(taddr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// kind::f16 (BF16 inputs, fp32 accumulate) 256-row MMA over the CTA pair, K = 16 per instruction; descriptors as (lo, hi) words
+__device__ __forceinline__ void mma_bf16_cg2_w(uint32_t d_tmem, uint32_t alo, uint32_t ahi, uint32_t blo, uint32_t bhi, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t"
+        "mov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %5, p;\n\t}"
+        :: "r"(d_tmem), "r"(alo), "r"(ahi), "r"(blo), "r"(bhi), "r"(idesc), "r"(accumulate) : "memory");
+}
+// instruction descriptor for kind::f16 with BF16 A and B, fp32 accumulate: [4,6) D = F32 | [7,10) A = BF16 (1) | [10,13) B = BF16 (1)
+__device__ __forceinline__ uint32_t idesc_bf16(int M, int N, int a_mn_major, int b_mn_major) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(a_mn_major & 1) << 15) | ((uint32_t)(b_mn_major & 1) << 16) |
+           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void sts128u(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ void stg128u(unsigned short* ptr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" :: "l"(ptr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// kind::f16 (BF16) 256-row MMA with the A operand in TENSOR MEMORY: 16 K elements = 8 columns (two BF16 per 32-bit cell, the
+// lower k in the low half)
+__device__ __forceinline__ void mma_bf16_cg2_ts(uint32_t d_tmem, uint32_t a_tmem, uint32_t blo, uint32_t bhi, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], db, %4, p;\n\t}"
+        :: "r"(d_tmem), "r"(a_tmem), "r"(blo), "r"(bhi), "r"(idesc), "r"(accumulate) : "memory");
+}
 
 // 256-row MMA over the CTA pair with the A operand in TENSOR MEMORY (each CTA's own 128 rows x 8 tf32 columns at `a_tmem`;
 // K-major by construction) and B in shared memory
@@ -106,8 +141,17 @@ __device__ __forceinline__ void stg256(float* ptr, const float (&r)[8]) {
 // addressing is pure issue-slot cost in a loop whose CUDA-core work (~800 issue cycles per chunk and scheduler) already
 // exceeds the chunk's MMA time (768 cycles at K = 64).  A TMEM store needs no proxy fence and no address arithmetic, and
 // the b-stage MMAs stop reading 4 KB of A per dispatch from shared memory.
-template <bool HSTEP, int NW, bool COST, int BN, bool YT>
+// CB (K = 256, two worker warps per quadrant): the two correction passes of every product, lo*hi and hi*lo, run
+// as kind::f16 BF16 MMAs (K = 16 per instruction: half the tensor time of a TF32 pass each) on BF16 forms of the operands —
+// bf = bf16(x) and lb = bf16(x - tf32(x)), which sit where the TF32 `lo` tile was (8 KB each: bf at +0, lb at +8 KB):
+//   D += A_lb * B_bf + A_bf * B_lb (2 + 2 BF16 MMAs)  +  A_hi * B_hi (4 TF32 MMAs)      — 8 instead of 12 MMA time units.
+// The correction terms are 2^-11 of the product and BF16 keeps 8 bits of each factor: ~2^-20 relative per product, the
+// level of the dropped lo*lo term.  BF16 tiles: MN-major = TMA boxes of 64 x 32 with the 128-byte swizzle (descriptor
+// layout SWIZZLE_128B, LBO 4096 between 64-wide boxes, SBO 1024 between 8-deep groups, 2048 B per K = 16 step);
+// K-major = 64-byte rows with the 64-byte swizzle (SWIZZLE_64B, SBO 512, 32 B per K = 16 step).
+template <bool HSTEP, int NW, bool COST, int BN, bool YT, bool CB>
 __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_constant__ FusedParams p) {
+    static_assert(!CB || (NW == 2 && !YT) || (NW == 4 && YT), "BF16 correction passes: K = 256 (two worker warps, quotient in shared memory) or K = 128 (four, quotient in tensor memory)");
     using FC = FCfg<NW>;
     constexpr int CW = FC::CW;
     constexpr int NCH = BN / 32;                       // 32-column chunks per S tile
@@ -147,6 +191,10 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&p.mapWhi); prefetch_tmap(&p.mapWlo); prefetch_tmap(&p.mapHhi); prefetch_tmap(&p.mapHlo);
         prefetch_tmap(&p.mapGhi); prefetch_tmap(&p.mapGlo); prefetch_tmap(&p.mapX);
+        if (CB) {
+            prefetch_tmap(&p.mapWbf); prefetch_tmap(&p.mapWlb); prefetch_tmap(&p.mapHbf); prefetch_tmap(&p.mapHlb);
+            prefetch_tmap(&p.mapGbf); prefetch_tmap(&p.mapGlb);
+        }
         for (int s = 0; s < F_XBUFS; ++s) { mbar_init(&xfull[s], 1); mbar_init(&xempty[s], FC::NARR); }
         for (int s = 0; s < F_STAGES; ++s) mbar_init(&full[s], 1);
         for (int s = 0; s < F_STAGES * F_EMPTY_WAYS; ++s) mbar_init(&empty[s], 1);
@@ -221,6 +269,17 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                     const uint32_t sH = HSTEP ? sA : sB;           // H: one K-major box (W step: BN/2 columns, H step: 128 lane rows)
                     const int w0 = HSTEP ? c0 + (int)rank * (BN / 2) : l0;
                     const int h0 = HSTEP ? l0 : c0 + (int)rank * (BN / 2);
+                    if (CB) {
+                        // hi tiles as TF32; the BF16 pair (bf, lb) in the two halves of the `lo` slot.  Same byte count.
+                        for (int j = 0; j < NBOX_W; ++j) tma_load_2d_cg2_a(sW + j * 4096, &p.mapWhi, fullc, w0 + 32 * j, r0, polW);
+                        tma_load_2d_cg2_a(sH, &p.mapHhi, fullc, r0, h0, polH);
+                        for (int j = 0; j < NBOX_W / 2; ++j) {
+                            tma_load_2d_cg2_a(sW + A_TILE_BYTES + j * 4096, &p.mapWbf, fullc, w0 + 64 * j, r0, polW);
+                            tma_load_2d_cg2_a(sW + A_TILE_BYTES + 8192 + j * 4096, &p.mapWlb, fullc, w0 + 64 * j, r0, polW);
+                        }
+                        tma_load_2d_cg2_a(sH + F_B_TILE, &p.mapHbf, fullc, r0, h0, polH);
+                        tma_load_2d_cg2_a(sH + F_B_TILE + 8192, &p.mapHlb, fullc, r0, h0, polH);
+                    } else
                     for (int h = 0; h < 2; ++h) {
                         const CUtensorMap* mW = h ? &p.mapWlo : &p.mapWhi;
                         for (int j = 0; j < NBOX_W; ++j)
@@ -242,6 +301,19 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                     const uint32_t sB = sb + stage * F_STAGE_BYTES + 2 * A_TILE_BYTES;
                     if (rank == 0) mbar_arrive_expect_tx_a(full_a + stage * 8, bytes_b);
                     const int n0 = c0 + s * 32;
+                    if (CB) {
+                        if (HSTEP) {
+                            tma_load_2d_cg2_a(sB, &p.mapGhi, fullc, n0, koff, polW);
+                            tma_load_2d_cg2_a(sB + F_B_TILE, &p.mapGbf, fullc, n0, koff, polW);
+                            tma_load_2d_cg2_a(sB + F_B_TILE + 8192, &p.mapGlb, fullc, n0, koff, polW);
+                        } else {
+                            for (int j = 0; j < bnh2 / 32; ++j) tma_load_2d_cg2_a(sB + j * 4096, &p.mapGhi, fullc, koff + 32 * j, n0, polH);
+                            for (int j = 0; j < bnh2 / 64; ++j) {
+                                tma_load_2d_cg2_a(sB + F_B_TILE + j * 4096, &p.mapGbf, fullc, koff + 64 * j, n0, polH);
+                                tma_load_2d_cg2_a(sB + F_B_TILE + 8192 + j * 4096, &p.mapGlb, fullc, koff + 64 * j, n0, polH);
+                            }
+                        }
+                    } else
                     for (int h = 0; h < 2; ++h) {
                         const CUtensorMap* mG = h ? &p.mapGlo : &p.mapGhi;
                         if (HSTEP) tma_load_2d_cg2_a(sB + h * F_B_TILE, mG, fullc, n0, koff, polW);
@@ -303,6 +375,26 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
         const uint32_t sAb = STEP_K,                   sBb = HSTEP ? STEP_K : STEP_MN;
         const uint32_t aHiW_a = (uint32_t)(dAa >> 32), bHiW_a = (uint32_t)(dBa >> 32), aLo_a = (uint32_t)dAa, bLo_a = (uint32_t)dBa;
         const uint32_t aHiW_b = (uint32_t)(dAb >> 32), bHiW_b = (uint32_t)(dBb >> 32), aLo_b = (uint32_t)dAb, bLo_b = (uint32_t)dBb;
+        // CB: the BF16 tiles (bf at the `lo` slot, lb 8 KB further): MN-major SWIZZLE_128B / K-major SWIZZLE_64B descriptors
+        const uint64_t eA_mn = smem_desc(sbase + A_TILE_BYTES, 4096u, 1024u, 2u), eA_k = smem_desc(sbase + A_TILE_BYTES, 16u, 512u, 4u);
+        const uint64_t eB_mn = smem_desc(sbase + 2 * A_TILE_BYTES + F_B_TILE, 4096u, 1024u, 2u), eB_k = smem_desc(sbase + 2 * A_TILE_BYTES + F_B_TILE, 16u, 512u, 4u);
+        constexpr uint32_t STEP16_MN = 2048u >> 4, STEP16_K = 32u >> 4, OFF_LB = 8192u >> 4;
+        const uint64_t eAa = HSTEP ? eA_k : eA_mn, eBa = HSTEP ? eB_mn : eB_k;
+        const uint64_t eAb = eA_k,                 eBb = HSTEP ? eB_k : eB_mn;
+        const uint32_t tAa = HSTEP ? STEP16_K : STEP16_MN, tBa = HSTEP ? STEP16_MN : STEP16_K;
+        const uint32_t tAb = STEP16_K,                     tBb = HSTEP ? STEP16_K : STEP16_MN;
+        const uint32_t idesc16_a = HSTEP ? idesc_bf16(2 * BM, BN, 0, 1) : idesc_bf16(2 * BM, BN, 1, 0);
+        const uint32_t idesc16_b = HSTEP ? idesc_bf16(2 * BM, p.Kv, 0, 0) : idesc_bf16(2 * BM, p.Kv, 0, 1);
+        // CB: the 8 MMA time units of one 32-deep block: lb*bf, bf*lb (BF16, K = 16), hi*hi (TF32, K = 8); small terms first
+        auto block_cb = [&](uint32_t d, uint32_t aH, uint32_t bH, uint32_t aW, uint32_t bW, uint32_t sa, uint32_t sb, uint32_t idesc,
+                            uint32_t a16, uint32_t b16, uint32_t a16W, uint32_t b16W, uint32_t ta, uint32_t tb, uint32_t idesc16, uint32_t acc) {
+            #pragma unroll
+            for (int ks = 0; ks < 2; ++ks) mma_bf16_cg2_w(d, a16 + OFF_LB + ks * ta, a16W, b16 + ks * tb, b16W, idesc16, ks == 0 ? acc : 1u);
+            #pragma unroll
+            for (int ks = 0; ks < 2; ++ks) mma_bf16_cg2_w(d, a16 + ks * ta, a16W, b16 + OFF_LB + ks * tb, b16W, idesc16, 1u);
+            #pragma unroll
+            for (int ks = 0; ks < BK / UK; ++ks) mma_tf32_cg2_w(d, aH + ks * sa, aW, bH + ks * sb, bW, idesc, 1u);
+        };
         // the 12 MMAs of one 32-deep block: lo*hi, hi*lo, hi*hi (small terms first)
         auto block = [&](uint32_t d, uint32_t aH, uint32_t aL, uint32_t bH, uint32_t bL, uint32_t aW, uint32_t bW,
                          uint32_t sa, uint32_t sb, uint32_t idesc, uint32_t acc) {
@@ -325,6 +417,9 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                 const uint32_t so = (uint32_t)(stage * F_STAGE_BYTES) >> 4;
                 const uint32_t aH = aLo_a + so, aL = aH + (A_TILE_BYTES >> 4), bH = bLo_a + so, bL = bH + (F_B_TILE >> 4);
                 if (elect_one()) {
+                    if (CB) block_cb(tmem_S + b * (uint32_t)BN, aH, bH, aHiW_a, bHiW_a, sAa, sBa, idesc_a, (uint32_t)eAa + so, (uint32_t)eBa + so,
+                                     (uint32_t)(eAa >> 32), (uint32_t)(eBa >> 32), tAa, tBa, idesc16_a, kb == 0 ? 0u : 1u);
+                    else
                     block(tmem_S + b * (uint32_t)BN, aH, aL, bH, bL, aHiW_a, bHiW_a, sAa, sBa, idesc_a, kb == 0 ? 0u : 1u);
                     mma_commit_cg2_a(empty_of(stage, use), (uint16_t)3);
                     if (kb == KB - 1) mma_commit_cg2_a(sfull_a + b * 8, (uint16_t)3);
@@ -350,12 +445,26 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                         const uint32_t yH = tmem_S + (gb % (uint32_t)SBUF) * (uint32_t)BN + (uint32_t)(c * 32);
                         const uint32_t yL = tmem_base + F_YT_COL + (yctr & (F_YT_SLOTS - 1u)) * 32u;
                         const uint32_t acc0 = in_period == 1 ? 0u : 1u;
+                        if (CB) {
+                            // the ring slot holds the BF16 forms, packed two per cell: bf in columns 0..15, lb in columns 16..31
+                            const uint32_t g16 = (uint32_t)eBb + so, g16W = (uint32_t)(eBb >> 32);
+                            #pragma unroll
+                            for (int ks = 0; ks < 2; ++ks) mma_bf16_cg2_ts(tmem_P, yL + 16u + ks * 8u, g16 + ks * tBb, g16W, idesc16_b, ks == 0 ? acc0 : 1u);
+                            #pragma unroll
+                            for (int ks = 0; ks < 2; ++ks) mma_bf16_cg2_ts(tmem_P, yL + ks * 8u, g16 + OFF_LB + ks * tBb, g16W, idesc16_b, 1u);
+                            #pragma unroll
+                            for (int ks = 0; ks < BK / UK; ++ks) mma_tf32_cg2_ts(tmem_P, yH + ks * UK, bH + ks * sBb, bHiW_b, idesc_b, 1u);
+                        } else {
                         #pragma unroll
                         for (int ks = 0; ks < BK / UK; ++ks) mma_tf32_cg2_ts(tmem_P, yL + ks * UK, bH + ks * sBb, bHiW_b, idesc_b, ks == 0 ? acc0 : 1u);
                         #pragma unroll
                         for (int ks = 0; ks < BK / UK; ++ks) mma_tf32_cg2_ts(tmem_P, yH + ks * UK, bL + ks * sBb, bHiW_b, idesc_b, 1u);
                         #pragma unroll
                         for (int ks = 0; ks < BK / UK; ++ks) mma_tf32_cg2_ts(tmem_P, yH + ks * UK, bH + ks * sBb, bHiW_b, idesc_b, 1u);
+                        }
+                    } else if (CB) {
+                        block_cb(tmem_P, aH, bH, aHiW_b, bHiW_b, sAb, sBb, idesc_b, (uint32_t)eAb + so, (uint32_t)eBb + so,
+                                 (uint32_t)(eAb >> 32), (uint32_t)(eBb >> 32), tAb, tBb, idesc16_b, in_period == 1 ? 0u : 1u);
                     } else
                     block(tmem_P, aH, aL, bH, bL, aHiW_b, bHiW_b, sAb, sBb, idesc_b, in_period == 1 ? 0u : 1u);
                     mma_commit_cg2_a(empty_of(stage, use), (uint16_t)3);
@@ -441,6 +550,13 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
             const int sp = (t / p.tiles_l) % p.nsplit;
             double cost_item = 0.0;
             int nt0, nt1; tile_range(t, nt0, nt1);
+            if (HSTEP && p.nsplit == 1 && !p.defer && row_ok) {
+                // the item's epilogue reads this thread's 128 bytes of H per accumulator chunk; H was last touched an iteration
+                // ago (DRAM by now): pull the lines into L2 while the item's tiles are computed
+                #pragma unroll
+                for (int cc = 0; cc < FC::ACC; ++cc)
+                    if (h + NW * cc < nchP) prefetch_l2(p.H + (size_t)l * (uint32_t)p.ldH + koff + (h + NW * cc) * 32);
+            }
             #pragma unroll
             for (int cc = 0; cc < FC::ACC; ++cc)
                 #pragma unroll
@@ -523,6 +639,12 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                         const uint32_t ys = yctr & (F_YT_SLOTS - 1u);
                         mbar_wait_a(yempty_a + ys * 8, ((yctr >> 2) & 1u) ^ 1u, p.err, 19);
                         tc_fence_after();
+                        if (CB) {        // BF16 forms of this thread's 8 elements, packed: bf -> cells 4h.., lb -> cells 16 + 4h.. of the slot
+                            const uint32_t cell = laneY - (uint32_t)(h * CW) + ys * 32u + (uint32_t)(h * (CW / 2));
+                            tmem_st_x4(cell, pack_bf16x2(z[0], z[1]), pack_bf16x2(z[2], z[3]), pack_bf16x2(z[4], z[5]), pack_bf16x2(z[6], z[7]));
+                            tmem_st_x4(cell + 16u, pack_bf16x2(__uint_as_float(zl[0]), __uint_as_float(zl[1])), pack_bf16x2(__uint_as_float(zl[2]), __uint_as_float(zl[3])),
+                                       pack_bf16x2(__uint_as_float(zl[4]), __uint_as_float(zl[5])), pack_bf16x2(__uint_as_float(zl[6]), __uint_as_float(zl[7])));
+                        } else
                         tmem_st_cols(laneY + ys * 32u, zl);
                         tmem_st_wait();
                         tc_fence_before();
@@ -530,6 +652,26 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                     // the ring slot of this b-stage must have been released by the MMAs that last read it
                     { uint32_t par; const uint32_t eb = empty_prev(stage, use, par); mbar_wait_a(eb, par, p.err, 19); }
                     const uint32_t hi_base = sb + stage * (uint32_t)F_STAGE_BYTES + row_off;
+                    if (CB) {
+                        // hi as a TF32 tile (K-major, 128-byte swizzle); bf = bf16(z) and lb = bf16(z - hi) as BF16 tiles where the lo
+                        // tile was (K-major: 64-byte rows, 8-row groups of 512 B, 16-byte chunk index XOR (row / 2) mod 4)
+                        const uint32_t b16 = sb + stage * (uint32_t)F_STAGE_BYTES + (uint32_t)A_TILE_BYTES + (row >> 3) * 512u + (row & 7u) * 64u;
+                        const uint32_t sw64 = (row >> 1) & 3u;
+                        #pragma unroll
+                        for (int v = 0; v < CW / 8; ++v) {
+                            float hv[8], lv[8];
+                            #pragma unroll
+                            for (int e = 0; e < 8; ++e) tf32_split_fast(z[8 * v + e], hv[e], lv[e]);
+                            const uint32_t a0 = hi_base + ((((uint32_t)((CW / 4) * h + 2 * v)) ^ sw) << 4);
+                            const uint32_t a1 = hi_base + ((((uint32_t)((CW / 4) * h + 2 * v + 1)) ^ sw) << 4);
+                            sts128(a0, make_float4(hv[0], hv[1], hv[2], hv[3]));
+                            sts128(a1, make_float4(hv[4], hv[5], hv[6], hv[7]));
+                            const uint32_t c16 = b16 + ((((uint32_t)((CW / 8) * h + v)) ^ sw64) << 4);
+                            sts128u(c16, pack_bf16x2(z[8 * v], z[8 * v + 1]), pack_bf16x2(z[8 * v + 2], z[8 * v + 3]),
+                                    pack_bf16x2(z[8 * v + 4], z[8 * v + 5]), pack_bf16x2(z[8 * v + 6], z[8 * v + 7]));
+                            sts128u(c16 + 8192u, pack_bf16x2(lv[0], lv[1]), pack_bf16x2(lv[2], lv[3]), pack_bf16x2(lv[4], lv[5]), pack_bf16x2(lv[6], lv[7]));
+                        }
+                    } else {
                     #pragma unroll
                     for (int v = 0; v < CW / 4; ++v) {
                         float4 hv, lv;
@@ -538,6 +680,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                         const uint32_t a = hi_base + ((((uint32_t)((CW / 4) * h + v)) ^ sw) << 4);
                         sts128(a, hv);
                         sts128(a + (uint32_t)A_TILE_BYTES, lv);
+                    }
                     }
                     fence_proxy_async_smem();
                     }
@@ -625,6 +768,11 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                                         tf32_split(hn[e], hh[e], hl[e]);
                                     }
                                     stg256(p.H + o, hn); stg256(p.Hhi + o, hh); stg256(p.Hlo + o, hl);
+                                    if (CB) {
+                                        stg128u(p.Hbf + o, pack_bf16x2(hn[0], hn[1]), pack_bf16x2(hn[2], hn[3]), pack_bf16x2(hn[4], hn[5]), pack_bf16x2(hn[6], hn[7]));
+                                        stg128u(p.Hlb + o, pack_bf16x2(hn[0] - hh[0], hn[1] - hh[1]), pack_bf16x2(hn[2] - hh[2], hn[3] - hh[3]),
+                                                pack_bf16x2(hn[4] - hh[4], hn[5] - hh[5]), pack_bf16x2(hn[6] - hh[6], hn[7] - hh[7]));
+                                    }
                                 }
                             }
                         }
@@ -662,13 +810,13 @@ int num_sms_f() {
     return n;
 }
 
-template <bool HSTEP, int NW, bool COST, int BN, bool YT>
+template <bool HSTEP, int NW, bool COST, int BN, bool YT, bool CB = false>
 void launch_fused_nw(const FusedParams& p, cudaStream_t st) {
     // function attributes are per device: one host thread per GPU may launch the same instantiation
     static std::atomic<unsigned long long> configured{0};            // bit d: done on device d
     int dev = 0; CUDA_CHECK(cudaGetDevice(&dev));
     if (!(configured.load(std::memory_order_acquire) >> (dev & 63) & 1ull)) {
-        CUDA_CHECK(cudaFuncSetAttribute(k_fused<HSTEP, NW, COST, BN, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_BYTES));
+        CUDA_CHECK(cudaFuncSetAttribute(k_fused<HSTEP, NW, COST, BN, YT, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_BYTES));
         configured.fetch_or(1ull << (dev & 63), std::memory_order_release);
     }
     cudaLaunchConfig_t cfg{};
@@ -689,13 +837,13 @@ void launch_fused_nw(const FusedParams& p, cudaStream_t st) {
         const int sms = num_sms_f();
         cfg.gridDim = dim3(2u * (unsigned)(sms / 2), 1, 1);
         int n = 0;
-        CUDA_CHECK(cudaOccupancyMaxActiveClusters(&n, k_fused<HSTEP, NW, COST, BN, YT>, &cfg));
+        CUDA_CHECK(cudaOccupancyMaxActiveClusters(&n, k_fused<HSTEP, NW, COST, BN, YT, CB>, &cfg));
         NMF_CHECK(n > 0, "no CTA pair of the fused half-iteration kernel fits on this device");
         max_pairs.store(std::min(n, sms / 2));
     }
     const long long items = (long long)p.tiles_l * p.nsplit * p.nbatch;
     cfg.gridDim = dim3(2u * (unsigned)std::min<long long>(items, max_pairs.load()), 1, 1);
-    CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_fused<HSTEP, NW, COST, BN, YT>, p));
+    CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_fused<HSTEP, NW, COST, BN, YT, CB>, p));
     CUDA_CHECK_LAUNCH();
 }
 
@@ -703,11 +851,15 @@ template <bool HSTEP, bool COST>
 void launch_fused_t(const FusedParams& p, cudaStream_t st) {
     // the quotient in tensor memory (ytmem) is instantiated for the K <= 128 default (4 worker warps per quadrant) only
     if (p.nw == 4) {
-        if (p.ytmem) {
+        if (p.ytmem && p.corr) {
+            if (p.bn == F_BN_DB) launch_fused_nw<HSTEP, 4, COST, F_BN_DB, true, true>(p, st); else launch_fused_nw<HSTEP, 4, COST, F_BN, true, true>(p, st);
+        } else if (p.ytmem) {
             if (p.bn == F_BN_DB) launch_fused_nw<HSTEP, 4, COST, F_BN_DB, true>(p, st); else launch_fused_nw<HSTEP, 4, COST, F_BN, true>(p, st);
         } else {
             if (p.bn == F_BN_DB) launch_fused_nw<HSTEP, 4, COST, F_BN_DB, false>(p, st); else launch_fused_nw<HSTEP, 4, COST, F_BN, false>(p, st);
         }
+    } else if (p.corr) {
+        if (p.bn == F_BN_DB) launch_fused_nw<HSTEP, 2, COST, F_BN_DB, false, true>(p, st); else launch_fused_nw<HSTEP, 2, COST, F_BN, false, true>(p, st);
     } else {
         if (p.bn == F_BN_DB) launch_fused_nw<HSTEP, 2, COST, F_BN_DB, false>(p, st); else launch_fused_nw<HSTEP, 2, COST, F_BN, false>(p, st);
     }
@@ -718,6 +870,8 @@ void launch_fused_t(const FusedParams& p, cudaStream_t st) {
 void launch_fused(bool hstep, bool cost, const FusedParams& p, cudaStream_t st) {
     NMF_CHECK(p.nw == 2 || (p.nw == 4 && p.Kv <= 128), "fused kernel: 4 worker warps per quadrant need a P tile of <= 128 columns");
     NMF_CHECK(!cost || hstep, "fused kernel: only the H step carries the cost");
+    NMF_CHECK(!p.corr || (p.nw == 2 && p.Kv == 256) || (p.nw == 4 && p.ytmem && p.Kv == 128),
+              "fused kernel: BF16 correction passes need K = 256, or K = 128 with the quotient in tensor memory");
     NMF_CHECK(!p.ytmem || (p.nw == 4 && p.Kv <= 128), "fused kernel: the quotient fits in tensor memory only beside a P tile of <= 128 columns");
     if (hstep) { if (cost) launch_fused_t<true, true>(p, st); else launch_fused_t<true, false>(p, st); }
     else launch_fused_t<false, false>(p, st);

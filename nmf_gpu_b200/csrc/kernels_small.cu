@@ -94,12 +94,25 @@ __global__ void k_fill_planted(float* __restrict__ x, int rows, int cols, int ld
     }
 }
 
-__global__ void k_split_tf32(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo, size_t n) {
+// The BF16 forms of the correction operands: bf = bf16(x), lb = bf16(x - tf32(x)), round to nearest.
+// Four consecutive elements as one 8-byte store each.
+__device__ __forceinline__ void store_bf16_pair4(unsigned short* __restrict__ bf, unsigned short* __restrict__ lb, size_t e,
+                                                 const float4& v, const float4& h) {
+    *reinterpret_cast<uint2*>(bf + e) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+    *reinterpret_cast<uint2*>(lb + e) = make_uint2(pack_bf16x2(v.x - h.x, v.y - h.y), pack_bf16x2(v.z - h.z, v.w - h.w));
+}
+
+__global__ void k_split_tf32(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo, size_t n,
+                             unsigned short* __restrict__ bf, unsigned short* __restrict__ lb) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         float h, l;
         tf32_split(x[i], h, l);
         hi[i] = h;
         lo[i] = l;
+        if (bf != nullptr) {
+            bf[i] = (unsigned short)(pack_bf16x2(x[i], x[i]) & 0xffffu);
+            lb[i] = (unsigned short)(pack_bf16x2(x[i] - h, x[i] - h) & 0xffffu);
+        }
     }
 }
 
@@ -171,7 +184,8 @@ __global__ void __launch_bounds__(256) k_rowsum_partial(const float* __restrict_
 // W update: one thread per 4 consecutive rows of one column (float4, ld is a multiple of 32).
 __global__ void __launch_bounds__(256) k_update_w(float* __restrict__ W, float* __restrict__ Whi, float* __restrict__ Wlo,
                                                   const float* __restrict__ P, int nsplit, size_t split_stride,
-                                                  const float* __restrict__ sumH, int Mv, int Kv, int divide) {
+                                                  const float* __restrict__ sumH, int Mv, int Kv, int divide,
+                                                  unsigned short* __restrict__ Wbf, unsigned short* __restrict__ Wlb) {
     pdl_sync();
     const size_t total4 = (size_t)Mv * Kv / 4;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
@@ -195,6 +209,7 @@ __global__ void __launch_bounds__(256) k_update_w(float* __restrict__ W, float* 
             tf32_split(w.z, h.z, l.z); tf32_split(w.w, h.w, l.w);
             *reinterpret_cast<float4*>(Whi + e) = h;
             *reinterpret_cast<float4*>(Wlo + e) = l;
+            if (Wbf != nullptr) store_bf16_pair4(Wbf, Wlb, e, w, h);
         }
     }
 }
@@ -212,7 +227,8 @@ __device__ __forceinline__ float block_sum_512(float v, float* red) {      // ev
 __global__ void __launch_bounds__(512) k_update_w_col(float* __restrict__ W, float* __restrict__ Whi, float* __restrict__ Wlo,
                                                       const float* __restrict__ P, int nsplit, size_t split_stride,
                                                       float* __restrict__ sumH, const float* __restrict__ rs_partials, int rs_blocks,
-                                                      int Mv, int Kv, int divide, float* __restrict__ sumW, int refcompat) {
+                                                      int Mv, int Kv, int divide, float* __restrict__ sumW, int refcompat,
+                                                      unsigned short* __restrict__ Wbf, unsigned short* __restrict__ Wlb) {
     pdl_sync();
     __shared__ float red[16];
     const int k = blockIdx.x;
@@ -243,6 +259,7 @@ __global__ void __launch_bounds__(512) k_update_w_col(float* __restrict__ W, flo
             tf32_split(w.z, h.z, l.z); tf32_split(w.w, h.w, l.w);
             *reinterpret_cast<float4*>(Whi + e) = h;
             *reinterpret_cast<float4*>(Wlo + e) = l;
+            if (Wbf != nullptr) store_bf16_pair4(Wbf, Wlb, e, w, h);
         }
         if (refcompat) {                                         // the reference's stale-read tail: rows m mod 64 in {0,1,2,4,8,16,32}
             cs += (ref_sum_mask(m) ? w.x : 0.0f) + (ref_sum_mask(m + 1) ? w.y : 0.0f) + (ref_sum_mask(m + 2) ? w.z : 0.0f) +
@@ -265,7 +282,8 @@ template <bool ROWSUM>
 __global__ void __launch_bounds__(256) k_update_h(float* __restrict__ H, float* __restrict__ Hhi, float* __restrict__ Hlo,
                                                   const float* __restrict__ P, int nsplit, size_t split_stride,
                                                   const float* __restrict__ sumW, int Kv, size_t total4,
-                                                  float* __restrict__ rs_partials, long long n_offset, int refcompat) {
+                                                  float* __restrict__ rs_partials, long long n_offset, int refcompat,
+                                                  unsigned short* __restrict__ Hbf, unsigned short* __restrict__ Hlb) {
     pdl_sync();
     float4 rs = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
@@ -288,6 +306,7 @@ __global__ void __launch_bounds__(256) k_update_h(float* __restrict__ H, float* 
             tf32_split(h.z, hi.z, lo.z); tf32_split(h.w, hi.w, lo.w);
             *reinterpret_cast<float4*>(Hhi + e) = hi;
             *reinterpret_cast<float4*>(Hlo + e) = lo;
+            if (Hbf != nullptr) store_bf16_pair4(Hbf, Hlb, e, h, hi);
         }
         if (ROWSUM && (!refcompat || ref_sum_mask(n_offset + (long long)(e / (size_t)Kv)))) {
             rs.x += h.x; rs.y += h.y; rs.z += h.z; rs.w += h.w;
@@ -487,9 +506,9 @@ void launch_fill_planted(float* x, int rows, int cols, int ld, long long col_off
     CUDA_CHECK_LAUNCH();
 }
 
-void launch_split_tf32(const float* x, float* hi, float* lo, size_t n, cudaStream_t st) {
+void launch_split_tf32(const float* x, float* hi, float* lo, size_t n, cudaStream_t st, unsigned short* bf, unsigned short* lb) {
     if (n == 0) return;
-    k_split_tf32<<<grid_for(n, 256), 256, 0, st>>>(x, hi, lo, n);
+    k_split_tf32<<<grid_for(n, 256), 256, 0, st>>>(x, hi, lo, n, bf, lb);
     CUDA_CHECK_LAUNCH();
 }
 
@@ -562,25 +581,26 @@ void rowsum_noalloc(const float* H_dev, int K, int N, float* sumH_dev, cudaStrea
 bool update_w_by_column(const Dims& d, int nsplit) { return d.szW() * (size_t)(nsplit + 4) * 4 <= ((size_t)64 << 20); }
 
 bool launch_update_w(float* W, float* Whi, float* Wlo, const float* P, int nsplit, size_t split_stride,
-                     float* sumH, const Dims& d, cudaStream_t st, const float* rs_partials, int rs_blocks, float* sumW_out) {
+                     float* sumH, const Dims& d, cudaStream_t st, const float* rs_partials, int rs_blocks, float* sumW_out,
+                     unsigned short* Wbf, unsigned short* Wlb) {
     if (update_w_by_column(d, nsplit)) {
         launch_k(k_update_w_col, dim3(d.Kv), dim3(512), 0, st, W, Whi, Wlo, P, nsplit, split_stride, sumH, rs_partials, rs_blocks,
-                 d.Mv, d.Kv, d.w_divide, sumW_out, d.refcompat);
+                 d.Mv, d.Kv, d.w_divide, sumW_out, d.refcompat, Wbf, Wlb);
         return sumW_out != nullptr;
     }
     NMF_CHECK(rs_partials == nullptr, "launch_update_w: fold the row-sum partials first for this shape");
     launch_k(k_update_w, dim3(grid_for(d.szW() / 4, 256)), dim3(256), 0, st, W, Whi, Wlo, P, nsplit, split_stride, (const float*)sumH,
-             d.Mv, d.Kv, d.w_divide);
+             d.Mv, d.Kv, d.w_divide, Wbf, Wlb);
     return false;
 }
 
 int launch_update_h(float* H, float* Hhi, float* Hlo, const float* P, int nsplit, size_t split_stride,
-                    const float* sumW, const Dims& d, cudaStream_t st, float* rowsum_partials) {
+                    const float* sumW, const Dims& d, cudaStream_t st, float* rowsum_partials, unsigned short* Hbf, unsigned short* Hlb) {
     const size_t total4 = (size_t)d.Kv * d.Nv / 4;
     const int grid = grid_for(total4, 256);
     const bool rowsum = rowsum_partials != nullptr && d.Kv <= 1024 && 1024 % d.Kv == 0;   // every thread keeps the same 4 rows k over its loop
-    if (rowsum) launch_k(k_update_h<true>, dim3(grid), dim3(256), 0, st, H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4, rowsum_partials, d.n_offset, d.refcompat);
-    else        launch_k(k_update_h<false>, dim3(grid), dim3(256), 0, st, H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4, (float*)nullptr, 0ll, 0);
+    if (rowsum) launch_k(k_update_h<true>, dim3(grid), dim3(256), 0, st, H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4, rowsum_partials, d.n_offset, d.refcompat, Hbf, Hlb);
+    else        launch_k(k_update_h<false>, dim3(grid), dim3(256), 0, st, H, Hhi, Hlo, P, nsplit, split_stride, sumW, d.Kv, total4, (float*)nullptr, 0ll, 0, Hbf, Hlb);
     return rowsum ? grid : 0;
 }
 

@@ -76,6 +76,8 @@ nmf_session_impl::~nmf_session_impl() {
     if (nccl) nccl_destroy(nccl);
     float* fl[] = {W, H, X, Y, Whi, Wlo, Hhi, Hlo, sumW, packed, Psplit, Hpart, rowsum_partials, Hbak, Wfin, Hfin, tail_part};
     for (float* p : fl) if (p) cudaFree(p);
+    unsigned short* bl[] = {Wbf, Wlb, Hbf, Hlb};
+    for (unsigned short* p : bl) if (p) cudaFree(p);
     if (cost_partials) cudaFree(cost_partials);
     if (cost_dev) cudaFree(cost_dev);
     if (cost_host) cudaFreeHost(cost_host);
@@ -130,6 +132,12 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
             if (!umma::fused_both_wanted(d, opt.tf32_passes, tn) || (tn.keep_quotient && R == 1)) s->Y = dalloc<float>(d.szXa());
             s->Whi = dalloc<float>(d.szW()); s->Wlo = dalloc<float>(d.szW());
             s->Hhi = dalloc<float>(d.szHa()); s->Hlo = dalloc<float>(d.szHa());
+            if (umma::corr_bf16_wanted(d, opt.tf32_passes, tn)) {
+                s->Wbf = dalloc<unsigned short>(d.szW()); s->Wlb = dalloc<unsigned short>(d.szW());
+                s->Hbf = dalloc<unsigned short>(d.szHa()); s->Hlb = dalloc<unsigned short>(d.szHa());
+                CUDA_CHECK(cudaMemsetAsync(s->Hbf, 0, d.szHa() * 2, s->stream));      // the padding columns stay zero
+                CUDA_CHECK(cudaMemsetAsync(s->Hlb, 0, d.szHa() * 2, s->stream));
+            }
             s->n_cost_partials = umma::cost_partial_count(d, tn);
             s->n_cost_partials_fused = umma::fused_cost_partial_count(d, opt.tf32_passes, tn);
             // W step: the (at most 4) rows beyond the last whole 256-row block leave the fused kernel (common.hpp, launch_w_tail)
@@ -178,8 +186,8 @@ void session_need_quotient(nmf_session_impl& s) {
 static void refresh_splits(nmf_session_impl& s, bool w, bool h) {
     if (w) s.sumW_valid = false;          // every path that rewrites W from outside the iteration comes through here
     if (s.opt.engine != NMF_ENGINE_TCGEN05) return;
-    if (w) { launch_split_tf32(s.W, s.Whi, s.Wlo, s.d.szW(), s.stream); }
-    if (h) { launch_split_tf32(s.H, s.Hhi, s.Hlo, s.d.szH(), s.stream); }
+    if (w) { launch_split_tf32(s.W, s.Whi, s.Wlo, s.d.szW(), s.stream, s.Wbf, s.Wlb); }
+    if (h) { launch_split_tf32(s.H, s.Hhi, s.Hlo, s.d.szH(), s.stream, s.Hbf, s.Hlb); }
 }
 
 // Host (unpadded, column-major, rows x cols) -> a block of a padded device buffer (leading dimension ld) + clamp, as
@@ -425,7 +433,7 @@ static void iteration_head_fused_cost(nmf_session_impl& s, PhaseTimer* pt) {
 static void restore_h(nmf_session_impl& s) {
     s.rowsum_blocks = 0;              // partial row sums the abandoned H step may have left belong to the H being discarded
     CUDA_CHECK(cudaMemcpyAsync(s.H, s.Hbak, s.d.szHa() * 4, cudaMemcpyDeviceToDevice, s.stream));
-    launch_split_tf32(s.H, s.Hhi, s.Hlo, s.d.szH(), s.stream); count_launches(s, 1);
+    launch_split_tf32(s.H, s.Hhi, s.Hlo, s.d.szH(), s.stream, s.Hbf, s.Hlb); count_launches(s, 1);
 }
 
 void iteration_rest(nmf_session_impl& s, PhaseTimer* pt) {
@@ -499,7 +507,7 @@ static void w_half(nmf_session_impl& s, PhaseTimer* pt) {
     // (small problems: the same kernel leaves the column sums of the new W for the next H step, nmf.cu:134)
     PHASE(pt, PH_UPDW, {
         s.sumW_valid = launch_update_w(s.W, s.Whi, s.Wlo, P, nsplit, stride, s.sumH, d, s.stream,
-                                       fold_in_update ? s.rowsum_partials : nullptr, rs_blocks, s.sumW);
+                                       fold_in_update ? s.rowsum_partials : nullptr, rs_blocks, s.sumW, s.Wbf, s.Wlb);
         count_launches(s, 1);
     });
 }

@@ -23,6 +23,7 @@ struct Tuning {
     int fhsplit = 0;       // NMF_UMMA_FHSPLIT   forced row-split count of the fused H step (0: the cost model chooses)
     int fuse_nw = 0;       // NMF_UMMA_FUSE_NW   worker warps per TMEM quadrant of the fused kernels (0: 4 when Kv <= 128, else 2)
     int fh_defer = 0;      // NMF_UMMA_FH_DEFER  fused H step leaves the update to k_update_h even without a row split
+    int corr_bf16 = 1;     // NMF_CORR_BF16      fused kernels, K = 256: the two correction passes (lo*hi, hi*lo) as BF16 MMAs
     int fuse_yt = 1;       // NMF_UMMA_FUSE_YT   K <= 128: stage the quotient in tensor memory (0: in shared memory, as K > 128 does)
     int fuse_bn = 128;     // NMF_UMMA_FUSE_BN   S tile width of the fused kernels (128 double-buffered, or 256)
     int hsplit = 0;        // NMF_UMMA_HSPLIT    forced row-split count of the two-kernel H update (0: automatic)
@@ -55,6 +56,9 @@ struct nmf_session_impl {
     float *Y = nullptr;
     // TF32 splits of the small operands (tcgen05 engine)
     float *Whi = nullptr, *Wlo = nullptr, *Hhi = nullptr, *Hlo = nullptr;
+    // BF16 forms of the correction operands (fused kernels with K = 256): bf16(x) and bf16(x - tf32(x));
+    // nullptr when the session does not use them
+    unsigned short *Wbf = nullptr, *Wlb = nullptr, *Hbf = nullptr, *Hlb = nullptr;
     // sums and the packed allreduce buffer [ numerator P (Mv*Kv) | sumH (Kv) ]
     float *sumW = nullptr, *packed = nullptr, *sumH = nullptr /* = packed + Mv*Kv */;
     float *Psplit = nullptr; int nsplit = 1;      // split-N partial numerators (tcgen05 engine)
@@ -132,6 +136,7 @@ int   fused_cost_partial_count(const Dims& d, int passes, const Tuning& tn);   /
 bool  fused_both_wanted(const Dims& d, int passes, const Tuning& tn);
 bool  fused_shape_ok(int Kr, int passes, const Tuning& tn);   // Kr (one restart's padded K) is a multiple of 64 and <= 256
 unsigned int protocol_error(const nmf_session_impl& s);
+bool  corr_bf16_wanted(const Dims& d, int passes, const Tuning& tn);   // the session's fused kernels run their correction passes in BF16
 bool  fused_h_needs_part(const Dims& d, int passes, const Tuning& tn);   // the fused H step writes partial sums (row split or deferred update)
 // raw contraction for descriptor bring-up (nmf_dbg_gemm)
 void  dbg_gemm(int which, const float* dA, const float* dB, float* dC, int M, int N, int K, int passes,

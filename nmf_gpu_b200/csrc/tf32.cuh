@@ -31,4 +31,11 @@ __device__ __forceinline__ void tf32_split_fast(float v, float& hi, float& lo) {
     lo = v - hi;
 }
 
+// two floats -> packed bf16x2, round to nearest even: the LOW half holds `lo_elem` (the element at the lower address)
+__device__ __forceinline__ unsigned pack_bf16x2(float lo_elem, float hi_elem) {
+    unsigned r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_elem), "f"(lo_elem));
+    return r;
+}
+
 }  // namespace nmf

@@ -39,6 +39,9 @@ struct alignas(64) FusedParams {
     CUtensorMap mapWhi, mapWlo;      // W pair [Mv x R*Kv], MN-major boxes 32 x 32    (a-stages: A in the W step, B in the H step)
     CUtensorMap mapHhi, mapHlo;      // H pair [R*Kv x Nv], K-major boxes 32 x 128    (a-stages: B in the W step, A in the H step)
     CUtensorMap mapGhi, mapGlo;      // b-stage B: W step H pair, MN-major boxes 32 x 32; H step W pair, K-major boxes 32 x Kv/2
+    // corr (BF16 correction passes, K = 256): the same three operands as BF16 arrays — bf = bf16(x), lb = bf16(x - tf32(x)):
+    // MN-major boxes 64 x 32 (128-byte swizzle), K-major boxes 32 x rows (64-byte swizzle)
+    CUtensorMap mapWbf, mapWlb, mapHbf, mapHlb, mapGbf, mapGlb;
     CUtensorMap mapX;                // X [Mv x Nv]: W step boxes 128 m x 32 n (no swizzle), H step boxes 32 m x 128 n (128B swizzle)
     int Ldim, Cdim, Kv;              // extents of the lane-row and tile-column dimensions (W step Mv, Nv; H step Nv, Mv); Kv of ONE restart
     int tiles_l, nsplit, ntiles_c;   // 256-row blocks of L, splits of the C range, 256-wide tiles of C
@@ -57,6 +60,8 @@ struct alignas(64) FusedParams {
     int bn;                          // S tile width the launch runs with (256, or 128 double-buffered)
     int nw;                          // worker warps per TMEM lane quadrant (2 or 4)
     int ytmem;                       // the quotient chunk is staged in tensor memory (A operand of the second GEMM from TMEM); nw == 4 only
+    int corr;                        // 1: correction passes lo*hi and hi*lo run as kind::f16 BF16 MMAs (nw == 2, Kv == 256 only)
+    unsigned short* Hbf; unsigned short* Hlb;   // corr, H step with nsplit == 1: the BF16 forms of the new H
     int defer;                       // H step: store W'*Y sums to P even when nsplit == 1, k_update_h applies the update
     unsigned int* err;
 };

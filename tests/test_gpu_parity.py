@@ -187,6 +187,49 @@ def test_fused_kernel_variants(api, oracle, nw, bn, shape, monkeypatch):
     assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
 
 
+@pytest.mark.parametrize("bn", ["128", "256"])
+@pytest.mark.parametrize("shape", [(600, 1300, 256), (1024, 290, 256), (2100, 3000, 250)])
+def test_fused_bf16_correction_passes(api, oracle, shape, bn, monkeypatch):
+    """K = 256 fused kernels with the two correction passes of every product (lo*hi, hi*lo) issued as BF16 MMAs on
+    bf16(x) / bf16(x - tf32(x)) operand tiles (NMF_CORR_BF16=1): half-steps against the oracle at the usual
+    2e-5, against the 3xTF32 kernels, and 30 whole iterations with a cost check at the north-star tolerance"""
+    monkeypatch.setenv("NMF_UMMA_FUSE_BN", bn)
+    W, H, X = rand_problem(*shape, seed=23)
+    monkeypatch.setenv("NMF_CORR_BF16", "0")
+    H0 = api.dbg_h_step(W, H, X, api.options()); W0 = api.dbg_w_step(W, H, X, api.options())
+    monkeypatch.setenv("NMF_CORR_BF16", "1")
+    H1 = api.dbg_h_step(W, H, X, api.options())
+    assert max_rel(H1, oracle.h_step(W, H, X, "exact", acc64=True)) < 2e-5 and max_rel(H1, H0) < 1e-5
+    W1 = api.dbg_w_step(W, H, X, api.options())
+    assert max_rel(W1, oracle.w_step(W, H, X, "exact", acc64=True)) < 2e-5 and max_rel(W1, W0) < 1e-5
+    Wo, Ho, _, cost = oracle.update_div(W, H, X, 0.0, 30, "exact", acc64=True)
+    Wd, Hd = W.copy(order="F"), H.copy(order="F")
+    res = api.update_div(Wd, Hd, X, 1e-12, 30)
+    assert res.iterations == 30
+    assert max_rel(Wd, Wo) < 1e-4 and max_rel(Hd, Ho) < 1e-4
+    assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
+
+
+@pytest.mark.parametrize("shape", [(700, 1500, 128), (2049, 3000, 128), (520, 5000, 100)])
+def test_fused_bf16_correction_passes_k128(api, oracle, shape, monkeypatch):
+    """the same at K = 128 (NMF_CORR_BF16 bit 1): the quotient's BF16 forms go through TENSOR MEMORY, packed two per cell
+    in the lo ring slot, and the second GEMM's correction MMAs take them from there (kind::f16 with A in TMEM)"""
+    W, H, X = rand_problem(*shape, seed=29)
+    monkeypatch.setenv("NMF_CORR_BF16", "0")
+    H0 = api.dbg_h_step(W, H, X, api.options()); W0 = api.dbg_w_step(W, H, X, api.options())
+    monkeypatch.setenv("NMF_CORR_BF16", "3")
+    H1 = api.dbg_h_step(W, H, X, api.options())
+    assert max_rel(H1, oracle.h_step(W, H, X, "exact", acc64=True)) < 2e-5 and max_rel(H1, H0) < 1e-5
+    W1 = api.dbg_w_step(W, H, X, api.options())
+    assert max_rel(W1, oracle.w_step(W, H, X, "exact", acc64=True)) < 2e-5 and max_rel(W1, W0) < 1e-5
+    Wo, Ho, _, cost = oracle.update_div(W, H, X, 0.0, 30, "exact", acc64=True)
+    Wd, Hd = W.copy(order="F"), H.copy(order="F")
+    res = api.update_div(Wd, Hd, X, 1e-12, 30)
+    assert res.iterations == 30
+    assert max_rel(Wd, Wo) < 1e-4 and max_rel(Hd, Ho) < 1e-4
+    assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
+
+
 @pytest.mark.parametrize("fuse", ["0", "1"])
 @pytest.mark.parametrize("xs,ws", [(1e-30, 1.0), (1e-20, 1e12), (1e25, 1e-6), (1.0, 1e-18)])
 def test_quotient_extreme_scales(api, oracle, fuse, xs, ws, monkeypatch):
