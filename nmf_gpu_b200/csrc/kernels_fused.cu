@@ -187,6 +187,12 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
     const int items = per_batch * p.nbatch;
     const int KB = p.kblocks;
     const int bnh2 = p.Kv >> 1;                                   // P columns this CTA stages per b-stage
+    // WEAVE (p.weave, two S tiles): the ring carries the next tile's a-stages BETWEEN this tile's b-stages (chunk c is
+    // preceded by k blocks [c KB / nch, (c + 1) KB / nch)) instead of all of them first.  With the BF16 correction passes an
+    // a-stage's MMAs take 512 cycles for 48 KB of operands (94 B/clk, what one SM can draw from L2 at best) and a b-stage's
+    // 1024 cycles for 32 KB; woven, the demand is even (128 KB per 2048 cycles) and the quotient chunks are due one per
+    // 2048 cycles instead of four in a row at 1024.
+    const bool weave = SBUF == 2 && p.weave != 0;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&p.mapWhi); prefetch_tmap(&p.mapWlo); prefetch_tmap(&p.mapHhi); prefetch_tmap(&p.mapHlo);
@@ -245,25 +251,29 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
 
     if (warp < F_WORK_WARP0) {
       setmaxnreg_dec<FC::REGS_CTRL>();
-      if (warp == 0) {
+      if (warp == 0 || (warp == 3 && p.prod2)) {
         // ===================== TMA producer =====================
+        // p.prod2: warps 0 and 3 share the loads of every stage (part 0: the TF32 hi tiles and the barrier's expect_tx;
+        // part 1: the lo / BF16 tiles) — a stage's 7-11 TMA instructions are issued by one thread each, and that issue
+        // time sits on the path slot free -> data landed -> MMAs issued that bounds the a-stages with a 3-slot ring.
+        const bool part0 = warp == 0, part1 = (warp == 3) || !p.prod2;
         const uint64_t polW = l2_policy(p.hintW), polH = l2_policy(p.hintH);
         const uint32_t bytes_a = 2u * (2u * (uint32_t)A_TILE_BYTES + 2u * (uint32_t)((BN / 2) * BK * 4));   // both CTAs' W and H pairs
         const uint32_t bytes_b = 2u * 2u * (uint32_t)(bnh2 * BK * 4);                               // both CTAs' G chunk pairs
         const uint32_t full_r = mapa_u32(full_a, 0u);                                               // the leader's `full` barriers
         constexpr int NBOX_W = HSTEP ? (BN / 2) / 32 : BM / 32;     // 32-row MN-major boxes of W (A: lane rows; B: this CTA's half of the tile)
         uint32_t stage = 0, use = 0;
-        auto load_a = [&](const Cur& c) {                           // the KB a-stages of a tile: W and H pairs of k block s
+        auto load_a = [&](const Cur& c, int s0, int s1) {           // a-stages [s0, s1) of a tile: W and H pairs of k block s
             const int l0 = (c.t % p.tiles_l) * 2 * BM + (int)rank * BM;      // this CTA's lane rows
             const int c0 = c.tj * BN;
             const int koff = (c.t / per_batch) * p.Kv;                        // this restart's k range
-            for (int s = 0; s < KB; ++s) {
+            for (int s = s0; s < s1; ++s) {
                 { uint32_t par; const uint32_t eb = empty_prev(stage, use, par); mbar_wait_a(eb, par, p.err, 11); }
                 if (elect_one()) {
                     const uint32_t fullc = full_r + stage * 8;
                     const uint32_t sA = sb + stage * F_STAGE_BYTES;
                     const uint32_t sB = sA + 2 * A_TILE_BYTES;
-                    if (rank == 0) mbar_arrive_expect_tx_a(full_a + stage * 8, bytes_a);
+                    if (rank == 0 && part0) mbar_arrive_expect_tx_a(full_a + stage * 8, bytes_a);
                     const int r0 = koff + s * BK;
                     const uint32_t sW = HSTEP ? sB : sA;
                     const uint32_t sH = HSTEP ? sA : sB;           // H: one K-major box (W step: BN/2 columns, H step: 128 lane rows)
@@ -271,16 +281,21 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                     const int h0 = HSTEP ? l0 : c0 + (int)rank * (BN / 2);
                     if (CB) {
                         // hi tiles as TF32; the BF16 pair (bf, lb) in the two halves of the `lo` slot.  Same byte count.
+                        if (part0) {
                         for (int j = 0; j < NBOX_W; ++j) tma_load_2d_cg2_a(sW + j * 4096, &p.mapWhi, fullc, w0 + 32 * j, r0, polW);
                         tma_load_2d_cg2_a(sH, &p.mapHhi, fullc, r0, h0, polH);
+                        }
+                        if (part1) {
                         for (int j = 0; j < NBOX_W / 2; ++j) {
                             tma_load_2d_cg2_a(sW + A_TILE_BYTES + j * 4096, &p.mapWbf, fullc, w0 + 64 * j, r0, polW);
                             tma_load_2d_cg2_a(sW + A_TILE_BYTES + 8192 + j * 4096, &p.mapWlb, fullc, w0 + 64 * j, r0, polW);
                         }
                         tma_load_2d_cg2_a(sH + F_B_TILE, &p.mapHbf, fullc, r0, h0, polH);
                         tma_load_2d_cg2_a(sH + F_B_TILE + 8192, &p.mapHlb, fullc, r0, h0, polH);
+                        }
                     } else
                     for (int h = 0; h < 2; ++h) {
+                        if (!(h ? part1 : part0)) continue;
                         const CUtensorMap* mW = h ? &p.mapWlo : &p.mapWhi;
                         for (int j = 0; j < NBOX_W; ++j)
                             tma_load_2d_cg2_a(sW + h * A_TILE_BYTES + j * 4096, mW, fullc, w0 + 32 * j, r0, polW);
@@ -291,23 +306,27 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                 if (++stage == (uint32_t)F_STAGES) { stage = 0; ++use; }
             }
         };
-        auto load_b = [&](const Cur& c) {                           // the b-stages of a tile: G chunk (the Y chunk is written by the workers)
-            const int c0 = c.tj * BN, nch = chunks_of(c.tj);
+        auto load_b = [&](const Cur& c, int s0, int s1) {           // b-stages [s0, s1) of a tile: G chunk (the Y chunk is written by the workers)
+            const int c0 = c.tj * BN;
             const int koff = (c.t / per_batch) * p.Kv + (int)rank * bnh2;    // this restart's k range, this CTA's half of it
-            for (int s = 0; s < nch; ++s) {
+            for (int s = s0; s < s1; ++s) {
                 { uint32_t par; const uint32_t eb = empty_prev(stage, use, par); mbar_wait_a(eb, par, p.err, 11); }
                 if (elect_one()) {
                     const uint32_t fullc = full_r + stage * 8;
                     const uint32_t sB = sb + stage * F_STAGE_BYTES + 2 * A_TILE_BYTES;
-                    if (rank == 0) mbar_arrive_expect_tx_a(full_a + stage * 8, bytes_b);
+                    if (rank == 0 && part0) mbar_arrive_expect_tx_a(full_a + stage * 8, bytes_b);
                     const int n0 = c0 + s * 32;
                     if (CB) {
                         if (HSTEP) {
-                            tma_load_2d_cg2_a(sB, &p.mapGhi, fullc, n0, koff, polW);
+                            if (part0) tma_load_2d_cg2_a(sB, &p.mapGhi, fullc, n0, koff, polW);
+                            if (part1) {
                             tma_load_2d_cg2_a(sB + F_B_TILE, &p.mapGbf, fullc, n0, koff, polW);
                             tma_load_2d_cg2_a(sB + F_B_TILE + 8192, &p.mapGlb, fullc, n0, koff, polW);
+                            }
                         } else {
+                            if (part0)
                             for (int j = 0; j < bnh2 / 32; ++j) tma_load_2d_cg2_a(sB + j * 4096, &p.mapGhi, fullc, koff + 32 * j, n0, polH);
+                            if (part1)
                             for (int j = 0; j < bnh2 / 64; ++j) {
                                 tma_load_2d_cg2_a(sB + F_B_TILE + j * 4096, &p.mapGbf, fullc, koff + 64 * j, n0, polH);
                                 tma_load_2d_cg2_a(sB + F_B_TILE + 8192 + j * 4096, &p.mapGlb, fullc, koff + 64 * j, n0, polH);
@@ -315,6 +334,7 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                         }
                     } else
                     for (int h = 0; h < 2; ++h) {
+                        if (!(h ? part1 : part0)) continue;
                         const CUtensorMap* mG = h ? &p.mapGlo : &p.mapGhi;
                         if (HSTEP) tma_load_2d_cg2_a(sB + h * F_B_TILE, mG, fullc, n0, koff, polW);
                         else {
@@ -328,11 +348,21 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
             }
         };
         Cur cur, nxt; cur_init(cur); nxt = cur;
-        if (SBUF == 2 && cur_valid(nxt)) { load_a(nxt); cur_next(nxt); }
+        if (SBUF == 2 && cur_valid(nxt)) { load_a(nxt, 0, KB); cur_next(nxt); }
         while (cur_valid(cur)) {
-            if (SBUF == 2) { if (cur_valid(nxt)) { load_a(nxt); cur_next(nxt); } }
-            else load_a(cur);
-            load_b(cur);
+            const int nch = chunks_of(cur.tj);
+            if (weave) {                                            // next tile's a-stages spread between this tile's b-stages
+                const bool more = cur_valid(nxt);
+                for (int c = 0; c < nch; ++c) {
+                    if (more) load_a(nxt, c * KB / nch, (c + 1) * KB / nch);
+                    load_b(cur, c, c + 1);
+                }
+                if (more) cur_next(nxt);
+            } else {
+                if (SBUF == 2) { if (cur_valid(nxt)) { load_a(nxt, 0, KB); cur_next(nxt); } }
+                else load_a(cur, 0, KB);
+                load_b(cur, 0, nch);
+            }
             cur_next(cur);
         }
       } else if (warp == 2) {
@@ -407,11 +437,14 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
         };
         uint32_t stage = 0, use = 0;
         uint32_t ga = 0, gb = 0, pctr = 0, yctr = 0;
-        auto issue_a = [&]() {                                   // S tile ga (TMEM columns (ga % SBUF) * BN ..) = sum over the k blocks
+        auto issue_a = [&](int kb0, int kb1) {                   // S tile ga (TMEM columns (ga % SBUF) * BN ..) += k blocks [kb0, kb1)
+            if (kb0 >= kb1) return;
             const uint32_t b = ga % (uint32_t)SBUF;
-            mbar_wait_a(sempty_a + b * 8, ((ga / (uint32_t)SBUF) & 1u) ^ 1u, p.err, 12);   // the tile that last used this S buffer has been read
-            tc_fence_after();
-            for (int kb = 0; kb < KB; ++kb) {
+            if (kb0 == 0) {
+                mbar_wait_a(sempty_a + b * 8, ((ga / (uint32_t)SBUF) & 1u) ^ 1u, p.err, 12);   // the tile that last used this S buffer has been read
+                tc_fence_after();
+            }
+            for (int kb = kb0; kb < kb1; ++kb) {
                 mbar_wait_a(full_a + stage * 8, use & 1u, p.err, 13);
                 tc_fence_after();
                 const uint32_t so = (uint32_t)(stage * F_STAGE_BYTES) >> 4;
@@ -427,11 +460,12 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                 __syncwarp();
                 if (++stage == (uint32_t)F_STAGES) { stage = 0; ++use; }
             }
-            ++ga;
+            if (kb1 == KB) ++ga;
         };
-        auto issue_b = [&](int nch) {                            // P += Y chunk * G chunk for the tile's chunks
-            int in_period = 0;
-            for (int c = 0; c < nch; ++c) {
+        int in_period = 0;                                       // chunks of the tile accumulated into P since its last hand-over
+        auto issue_b = [&](int cb0, int cb1, int nch) {          // P += Y chunk * G chunk for chunks [cb0, cb1) of the tile
+            if (cb0 == 0) in_period = 0;
+            for (int c = cb0; c < cb1; ++c) {
                 if (in_period == 0) { mbar_wait_a(pempty_a, (pctr & 1u) ^ 1u, p.err, 14); }     // P drained by the workers
                 mbar_wait_a(full_a + stage * 8, use & 1u, p.err, 15);                               // G chunk landed
                 mbar_wait_a(yfull_a + (yctr & (F_YRING - 1)) * 8, (yctr / F_YRING) & 1u, p.err, 16);  // Y chunk written (both CTAs)
@@ -476,14 +510,24 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                 ++yctr;
                 if (++stage == (uint32_t)F_STAGES) { stage = 0; ++use; }
             }
-            ++gb;
+            if (cb1 == nch) ++gb;
         };
         Cur cur, nxt; cur_init(cur); nxt = cur;
-        if (SBUF == 2 && cur_valid(nxt)) { issue_a(); cur_next(nxt); }
+        if (SBUF == 2 && cur_valid(nxt)) { issue_a(0, KB); cur_next(nxt); }
         while (cur_valid(cur)) {
-            if (SBUF == 2) { if (cur_valid(nxt)) { issue_a(); cur_next(nxt); } }
-            else issue_a();
-            issue_b(chunks_of(cur.tj));
+            const int nch = chunks_of(cur.tj);
+            if (weave) {
+                const bool more = cur_valid(nxt);
+                for (int c = 0; c < nch; ++c) {
+                    if (more) issue_a(c * KB / nch, (c + 1) * KB / nch);
+                    issue_b(c, c + 1, nch);
+                }
+                if (more) cur_next(nxt);
+            } else {
+                if (SBUF == 2) { if (cur_valid(nxt)) { issue_a(0, KB); cur_next(nxt); } }
+                else issue_a(0, KB);
+                issue_b(0, nch, nch);
+            }
             cur_next(cur);
         }
       }
@@ -496,13 +540,18 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
         const uint32_t row = (uint32_t)(q * 32 + lane);                       // lane row inside this CTA's 128 x 32 A tile
         const uint32_t row_off = (row >> 3) * 1024u + (row & 7u) * 128u;      // K-major SWIZZLE_128B: 8-row groups of 1 KB,
         const uint32_t sw = row & 7u;                                         // 16-byte chunk index XOR (row mod 8)
-        const uint32_t laneS0 = tmem_S + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * CW);
+        const uint32_t laneS0 = tmem_S + ((uint32_t)(q * 32) << 16);         // + the column half (hx * CW) per access
         const uint32_t laneP = tmem_P + ((uint32_t)(q * 32) << 16);
         const uint32_t laneY = tmem_base + F_YT_COL + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * CW);   // YT: this warp's columns of a lo slot
         // this thread's X elements of a chunk.  W step: [column][lane row], no swizzle: 16 scalars 512 B apart.
         // H step: [lane row][32 columns] with the 128-byte swizzle: four 16-byte pieces of its own 128-byte row.
-        const uint32_t xoff = HSTEP ? xbuf_a + row * 128u
-                                    : xbuf_a + (uint32_t)(h * CW) * (uint32_t)(BM * 4) + row * 4u;
+        // (the column half hx * CW is added per access)
+        const uint32_t xoff = HSTEP ? xbuf_a + row * 128u : xbuf_a + row * 4u;
+        // ALT (p.alt, two worker warps per quadrant, quotient through shared memory): instead of half the columns of EVERY
+        // chunk, a warp takes ALL 32 columns of every other chunk (chunk parity = h) — the per-chunk costs that do not depend
+        // on the column count (the proxy fence that publishes the stores, the barrier waits and arrivals) are paid half as
+        // often per warp.  A handling warp arrives twice where the two halves' warps arrived once each.
+        const bool alt = (NW == 2 && !YT) && p.alt != 0;
         // the leader CTA's barriers these warps arrive on (shared::cluster addresses, computed once: mapa and the
         // special-register reads behind it sat on the worker -> MMA critical path of every chunk)
         const uint32_t yfull_r = mapa_u32(yfull_a, 0u), sempty_r = mapa_u32(sempty_a, 0u), pempty_r = mapa_u32(pempty_a, 0u);
@@ -541,6 +590,10 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
             stage += kb_mod; use += kb_div;
             if (stage >= (uint32_t)F_STAGES) { stage -= (uint32_t)F_STAGES; ++use; }
         };
+        auto skip_n = [&](uint32_t n) {                  // weave: the a-stages that precede one b-stage
+            stage += n % (uint32_t)F_STAGES; use += n / (uint32_t)F_STAGES;
+            if (stage >= (uint32_t)F_STAGES) { stage -= (uint32_t)F_STAGES; ++use; }
+        };
         if (SBUF == 2 && worker < items) skip_a();       // the first tile's a-stages lead the ring
         for (int t = worker; t < items; t += nworkers) {
             const int l = (t % p.tiles_l) * 2 * BM + rowoff;             // this thread's lane row (W step: m, H step: n)
@@ -565,33 +618,51 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                 const int nch = chunks_of(tj);
                 // ring order: SBUF == 1: this tile's a-stages, then its b-stages; SBUF == 2: the NEXT tile's a-stages
                 // (if there is a next tile) come before this tile's b-stages
-                if (SBUF == 1 || (tj + 1 < nt1) || (t + nworkers < items)) skip_a();
+                const bool more = SBUF == 1 || (tj + 1 < nt1) || (t + nworkers < items);
+                if (more && !weave) skip_a();
                 int in_period = 0;
                 float cost_tile = 0.0f;                  // <= 8 x CW terms in fp32, then into the item's double
                 const uint32_t sbuf = gw % (uint32_t)SBUF;
                 const uint32_t laneS = laneS0 + sbuf * (uint32_t)BN;
+                // the chunk after whose S read this warp releases the S tile: its last one (ALT: of its parity; none: chunk 0)
+                int rel_c = nch - 1;
+                if (alt && ((nch - 1) & 1) != h) rel_c = nch >= 2 ? nch - 2 : 0;
+                const int hh1 = alt ? 2 : h + 1;            // one past the last column half this warp reads of a chunk
                 mbar_wait_a(sfull_a + sbuf * 8, (gw / (uint32_t)SBUF) & 1u, p.err, 18);
                 tc_fence_after();
                 #pragma unroll 1
                 for (int c = 0; c < nch; ++c, ++yctr, ++xi) {
                     const uint32_t xs = xi & 1u;
-                    uint32_t r[CW];
-                    tmem_ld_cols(laneS + (uint32_t)(c * 32), r);
+                    const bool mine = !alt || ((c & 1) == h);
+                    if (weave && more) skip_n((uint32_t)((c + 1) * KB / nch - c * KB / nch));
+                    if (mine) {
                     mbar_wait_a(xfull_a + xs * 8, (xi >> 1) & 1u, p.err, 21);
+                    // phase 1: the quotient of this warp's columns of the chunk into registers — its own half, or (ALT) both
+                    // halves one after the other: all of it happens BEFORE the wait for the ring slot, which for a tile's first
+                    // chunks lasts through the next tile's a-stages
+                    constexpr int NH = (NW == 2 && !YT) ? 2 : 1;
+                    float z[NH][CW];
+                    #pragma unroll
+                    for (int hi_ = 0; hi_ < NH; ++hi_) {
+                    if (hi_ < (alt ? 2 : 1)) {
+                    const int hx = alt ? hi_ : h;
+                    uint32_t r[CW];
+                    tmem_ld_cols(laneS + (uint32_t)(c * 32 + hx * CW), r);
                     float x[CW];
                     if (HSTEP) {
                         #pragma unroll
                         for (int v = 0; v < CW / 4; ++v) {
-                            const float4 xv = lds128(xoff + xs * (uint32_t)F_XBUF_BYTES + ((((uint32_t)((CW / 4) * h + v)) ^ sw) << 4));
+                            const float4 xv = lds128(xoff + xs * (uint32_t)F_XBUF_BYTES + ((((uint32_t)((CW / 4) * hx + v)) ^ sw) << 4));
                             x[4 * v] = xv.x; x[4 * v + 1] = xv.y; x[4 * v + 2] = xv.z; x[4 * v + 3] = xv.w;
                         }
                     } else {
+                        const uint32_t xa = xoff + xs * (uint32_t)F_XBUF_BYTES + (uint32_t)(hx * CW) * (uint32_t)(BM * 4);
                         #pragma unroll
                         for (int jj = 0; jj < CW; ++jj)
-                            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x[jj]) : "r"(xoff + xs * (uint32_t)F_XBUF_BYTES + (uint32_t)(jj * BM * 4)));
+                            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x[jj]) : "r"(xa + (uint32_t)(jj * BM * 4)));
                     }
                     tmem_ld_wait();
-                    if (c == nch - 1) {                  // S is free for the next tile's a-stages
+                    if (c == rel_c && hx == hh1 - 1) {   // S is free for the next tile's a-stages
                         tc_fence_before();
                         __syncwarp();
                         if (elect_one()) mbar_arrive_cluster(sempty_r + sbuf * 8);
@@ -600,7 +671,6 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                     // residual correction (correctly rounded for normal quotients; x = 0 — zero-filled rows and columns
                     // beyond the matrix — gives exactly 0 and a quotient that underflows goes to 0 as x / y does); one check
                     // per thread and chunk sends huge or non-finite divisors and quotients (NaN fails the comparison) to the exact divide
-                    float z[CW];
                     float qmax = 0.0f;
                     #pragma unroll
                     for (int jj = 0; jj < CW; ++jj) {
@@ -609,14 +679,14 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                         asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(y));
                         const float q0 = x[jj] * rc;
                         qmax = fmaxf(qmax, fmaxf(q0, y));
-                        z[jj] = fmaf(fmaf(-y, q0, x[jj]), rc, q0);
+                        z[hi_][jj] = fmaf(fmaf(-y, q0, x[jj]), rc, q0);
                     }
                     if (!(qmax <= 1.0e30f)) {
                         #pragma unroll
-                        for (int jj = 0; jj < CW; ++jj) z[jj] = x[jj] / clampE(__uint_as_float(r[jj]));
+                        for (int jj = 0; jj < CW; ++jj) z[hi_][jj] = x[jj] / clampE(__uint_as_float(r[jj]));
                     }
                     if (COST) {                          // x (log x - log y) - x + y, the term of reduce1d_div (matrix.cu:593)
-                        const int cb = tj * BN + c * 32 + h * CW;
+                        const int cb = tj * BN + c * 32 + hx * CW;
                         #pragma unroll
                         for (int jj = 0; jj < CW; ++jj) {
                             if (row_log && cb + jj < p.Clog) {
@@ -625,23 +695,26 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                             }
                         }
                     }
+                    }
+                    }
+                    // phase 2: hand the chunk to the second GEMM
                     if (YT) {
                         uint32_t zh[CW], zl[CW];
                         #pragma unroll
                         for (int jj = 0; jj < CW; ++jj) {
                             float hv, lv;
-                            tf32_split_fast(z[jj], hv, lv);
+                            tf32_split_fast(z[0][jj], hv, lv);
                             zh[jj] = __float_as_uint(hv); zl[jj] = __float_as_uint(lv);
                         }
                         // hi: in place, over the S values this thread has just read (nobody else touches these lanes and columns)
-                        tmem_st_cols(laneS + (uint32_t)(c * 32), zh);
+                        tmem_st_cols(laneS + (uint32_t)(c * 32 + h * CW), zh);
                         // lo: ring slot yctr & 3, free once the b-stage that read it four chunks ago has retired (first round: passes)
                         const uint32_t ys = yctr & (F_YT_SLOTS - 1u);
                         mbar_wait_a(yempty_a + ys * 8, ((yctr >> 2) & 1u) ^ 1u, p.err, 19);
                         tc_fence_after();
                         if (CB) {        // BF16 forms of this thread's 8 elements, packed: bf -> cells 4h.., lb -> cells 16 + 4h.. of the slot
                             const uint32_t cell = laneY - (uint32_t)(h * CW) + ys * 32u + (uint32_t)(h * (CW / 2));
-                            tmem_st_x4(cell, pack_bf16x2(z[0], z[1]), pack_bf16x2(z[2], z[3]), pack_bf16x2(z[4], z[5]), pack_bf16x2(z[6], z[7]));
+                            tmem_st_x4(cell, pack_bf16x2(z[0][0], z[0][1]), pack_bf16x2(z[0][2], z[0][3]), pack_bf16x2(z[0][4], z[0][5]), pack_bf16x2(z[0][6], z[0][7]));
                             tmem_st_x4(cell + 16u, pack_bf16x2(__uint_as_float(zl[0]), __uint_as_float(zl[1])), pack_bf16x2(__uint_as_float(zl[2]), __uint_as_float(zl[3])),
                                        pack_bf16x2(__uint_as_float(zl[4]), __uint_as_float(zl[5])), pack_bf16x2(__uint_as_float(zl[6]), __uint_as_float(zl[7])));
                         } else
@@ -649,9 +722,19 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                         tmem_st_wait();
                         tc_fence_before();
                     } else {
+                    // EARLY DRAIN (p.drain_early): the ring slot of a tile's first b-stage follows the NEXT tile's a-stages, so the
+                    // workers sit here through most of an a-phase with this chunk's quotient in registers.  A period of P that
+                    // ended with the previous tile completed before those a-stages were even issued: draining it now, instead
+                    // of after this chunk's hand-off, takes it off the path slot free -> Y written -> b-stage issued (the MMA
+                    // warp waits for `pempty` before the tile's first b-stage).
+                    if (p.drain_early && pending) { drain(); pending = false; }
                     // the ring slot of this b-stage must have been released by the MMAs that last read it
                     { uint32_t par; const uint32_t eb = empty_prev(stage, use, par); mbar_wait_a(eb, par, p.err, 19); }
                     const uint32_t hi_base = sb + stage * (uint32_t)F_STAGE_BYTES + row_off;
+                    #pragma unroll
+                    for (int hi_ = 0; hi_ < NH; ++hi_) {
+                    if (hi_ < (alt ? 2 : 1)) {
+                    const int hx = alt ? hi_ : h;
                     if (CB) {
                         // hi as a TF32 tile (K-major, 128-byte swizzle); bf = bf16(z) and lb = bf16(z - hi) as BF16 tiles where the lo
                         // tile was (K-major: 64-byte rows, 8-row groups of 512 B, 16-byte chunk index XOR (row / 2) mod 4)
@@ -661,44 +744,57 @@ __global__ void __launch_bounds__(FCfg<NW>::NTHREADS, 1) k_fused(const __grid_co
                         for (int v = 0; v < CW / 8; ++v) {
                             float hv[8], lv[8];
                             #pragma unroll
-                            for (int e = 0; e < 8; ++e) tf32_split_fast(z[8 * v + e], hv[e], lv[e]);
-                            const uint32_t a0 = hi_base + ((((uint32_t)((CW / 4) * h + 2 * v)) ^ sw) << 4);
-                            const uint32_t a1 = hi_base + ((((uint32_t)((CW / 4) * h + 2 * v + 1)) ^ sw) << 4);
+                            for (int e = 0; e < 8; ++e) tf32_split_fast(z[hi_][8 * v + e], hv[e], lv[e]);
+                            const uint32_t a0 = hi_base + ((((uint32_t)((CW / 4) * hx + 2 * v)) ^ sw) << 4);
+                            const uint32_t a1 = hi_base + ((((uint32_t)((CW / 4) * hx + 2 * v + 1)) ^ sw) << 4);
                             sts128(a0, make_float4(hv[0], hv[1], hv[2], hv[3]));
                             sts128(a1, make_float4(hv[4], hv[5], hv[6], hv[7]));
-                            const uint32_t c16 = b16 + ((((uint32_t)((CW / 8) * h + v)) ^ sw64) << 4);
-                            sts128u(c16, pack_bf16x2(z[8 * v], z[8 * v + 1]), pack_bf16x2(z[8 * v + 2], z[8 * v + 3]),
-                                    pack_bf16x2(z[8 * v + 4], z[8 * v + 5]), pack_bf16x2(z[8 * v + 6], z[8 * v + 7]));
+                            const uint32_t c16 = b16 + ((((uint32_t)((CW / 8) * hx + v)) ^ sw64) << 4);
+                            sts128u(c16, pack_bf16x2(z[hi_][8 * v], z[hi_][8 * v + 1]), pack_bf16x2(z[hi_][8 * v + 2], z[hi_][8 * v + 3]),
+                                    pack_bf16x2(z[hi_][8 * v + 4], z[hi_][8 * v + 5]), pack_bf16x2(z[hi_][8 * v + 6], z[hi_][8 * v + 7]));
                             sts128u(c16 + 8192u, pack_bf16x2(lv[0], lv[1]), pack_bf16x2(lv[2], lv[3]), pack_bf16x2(lv[4], lv[5]), pack_bf16x2(lv[6], lv[7]));
                         }
                     } else {
                     #pragma unroll
                     for (int v = 0; v < CW / 4; ++v) {
                         float4 hv, lv;
-                        tf32_split_fast(z[4 * v + 0], hv.x, lv.x); tf32_split_fast(z[4 * v + 1], hv.y, lv.y);
-                        tf32_split_fast(z[4 * v + 2], hv.z, lv.z); tf32_split_fast(z[4 * v + 3], hv.w, lv.w);
-                        const uint32_t a = hi_base + ((((uint32_t)((CW / 4) * h + v)) ^ sw) << 4);
+                        tf32_split_fast(z[hi_][4 * v + 0], hv.x, lv.x); tf32_split_fast(z[hi_][4 * v + 1], hv.y, lv.y);
+                        tf32_split_fast(z[hi_][4 * v + 2], hv.z, lv.z); tf32_split_fast(z[hi_][4 * v + 3], hv.w, lv.w);
+                        const uint32_t a = hi_base + ((((uint32_t)((CW / 4) * hx + v)) ^ sw) << 4);
                         sts128(a, hv);
                         sts128(a + (uint32_t)A_TILE_BYTES, lv);
                     }
                     }
-                    fence_proxy_async_smem();
                     }
+                    }
+                    }
+                    if (!YT) fence_proxy_async_smem();
                     __syncwarp();
                     if (elect_one()) {
-                        mbar_arrive_cluster(yfull_r + ((yctr & (uint32_t)(F_YRING - 1)) << 3));
+                        const uint32_t yb = yfull_r + ((yctr & (uint32_t)(F_YRING - 1)) << 3);
+                        mbar_arrive_cluster(yb);
                         mbar_arrive_a(xempty_a + xs * 8);   // the X values were consumed by the math above
+                        if (alt) { mbar_arrive_cluster(yb); mbar_arrive_a(xempty_a + xs * 8); }   // for the warp that sat this chunk out
+                    }
+                    } else if (c == rel_c) {             // ALT, a tile with no chunk of this warp's parity: nothing of S to read
+                        tc_fence_before();
+                        __syncwarp();
+                        if (elect_one()) mbar_arrive_cluster(sempty_r + sbuf * 8);
                     }
                     if (++stage == (uint32_t)F_STAGES) { stage = 0; ++use; }
-                    // a period that ended one chunk ago: its MMAs ran while this chunk's quotient was computed
-                    if (pending) { drain(); pending = false; }
-                    if (++in_period == p.period) { in_period = 0; pending = true; }
+                    // a period that ended one chunk ago (ALT: one or two): its MMAs ran while this chunk's quotient was
+                    // computed.  A warp drains after a chunk it worked on; a second period never ends on an undrained one
+                    if (pending && mine) { drain(); pending = false; }
+                    if (++in_period == p.period) { in_period = 0; if (pending) drain(); pending = true; }
                 }
                 if (SBUF == 2) {
                     // the tile's last period is drained after the first quotient chunk of the next tile (or below, at the
                     // end of the work item): its MMAs are queued behind the next tile's a-stages
-                    if (in_period != 0) pending = true;
-                } else if (pending || in_period != 0) { drain(); pending = false; }   // overlaps the next tile's a-stages
+                    if (in_period != 0) { if (pending) drain(); pending = true; }
+                } else {                                 // overlaps the next tile's a-stages
+                    if (pending) { drain(); pending = false; }
+                    if (in_period != 0) drain();
+                }
                 ++gw;
                 if (COST) cost_item += (double)cost_tile;
             }

@@ -23,7 +23,11 @@ struct Tuning {
     int fhsplit = 0;       // NMF_UMMA_FHSPLIT   forced row-split count of the fused H step (0: the cost model chooses)
     int fuse_nw = 0;       // NMF_UMMA_FUSE_NW   worker warps per TMEM quadrant of the fused kernels (0: 4 when Kv <= 128, else 2)
     int fh_defer = 0;      // NMF_UMMA_FH_DEFER  fused H step leaves the update to k_update_h even without a row split
-    int corr_bf16 = 1;     // NMF_CORR_BF16      fused kernels, K = 256: the two correction passes (lo*hi, hi*lo) as BF16 MMAs
+    int corr_bf16 = 3;     // NMF_CORR_BF16      fused kernels: the two correction passes (lo*hi, hi*lo) as BF16 MMAs (bit 0: K = 256, bit 1: K = 128)
+    int weave = 0;         // NMF_UMMA_WEAVE     fused kernels, two S tiles: a- and b-stages interleaved in the ring (even L2 -> SM demand)
+    int prod2 = 0;         // NMF_UMMA_PROD2     fused kernels: warps 0 and 3 share the TMA loads of every ring stage
+    int drain_early = 0;   // NMF_UMMA_DRAIN_EARLY  fused kernels, quotient through shared memory: drain P before the ring-slot wait of a chunk, not after its hand-off
+    int fuse_alt = 0;      // NMF_UMMA_FUSE_ALT  two worker warps per quadrant (K > 128): a warp takes whole chunks in turn instead of half of every chunk
     int fuse_yt = 1;       // NMF_UMMA_FUSE_YT   K <= 128: stage the quotient in tensor memory (0: in shared memory, as K > 128 does)
     int fuse_bn = 128;     // NMF_UMMA_FUSE_BN   S tile width of the fused kernels (128 double-buffered, or 256)
     int hsplit = 0;        // NMF_UMMA_HSPLIT    forced row-split count of the two-kernel H update (0: automatic)

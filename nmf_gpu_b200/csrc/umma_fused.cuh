@@ -60,6 +60,10 @@ struct alignas(64) FusedParams {
     int bn;                          // S tile width the launch runs with (256, or 128 double-buffered)
     int nw;                          // worker warps per TMEM lane quadrant (2 or 4)
     int ytmem;                       // the quotient chunk is staged in tensor memory (A operand of the second GEMM from TMEM); nw == 4 only
+    int weave;                       // two S tiles: the next tile's a-stages are spread between this tile's b-stages in the ring
+    int prod2;                       // two TMA producer warps (0 and 3) share the loads of every ring stage
+    int drain_early;                 // quotient through shared memory: drain a pending period of P before waiting for the b-stage's ring slot
+    int alt;                         // nw == 2: a worker warp takes all 32 columns of every other chunk (else 16 columns of every chunk)
     int corr;                        // 1: correction passes lo*hi and hi*lo run as kind::f16 BF16 MMAs (nw == 2, Kv == 256 only)
     unsigned short* Hbf; unsigned short* Hlb;   // corr, H step with nsplit == 1: the BF16 forms of the new H
     int defer;                       // H step: store W'*Y sums to P even when nsplit == 1, k_update_h applies the update

@@ -13,7 +13,11 @@ KEEP = ["dram__bytes_read.sum", "dram__bytes_write.sum", "dram__sectors_read.sum
         "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
         "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
         "smsp__average_warp_latency_per_inst_issued.ratio", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
-        "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "smsp__inst_executed.sum"]
+        "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "smsp__inst_executed.sum",
+        # bytes arriving at the SMs from L2 (the operand-delivery bound of the BF16-correction kernels)
+        "l1tex__m_xbar2l1tex_read_bytes.sum", "l1tex__m_xbar2l1tex_read_bytes.sum.per_second",
+        "l1tex__m_xbar2l1tex_read_bytes.sum.pct_of_peak_sustained_elapsed", "derived__lts__lts2xbar_bytes.sum.per_second",
+        "lts__lts2xbar_cycles_active.avg.pct_of_peak_sustained_elapsed"]
 out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(l for l in out.splitlines() if l.startswith('"')))
 hdr, units, data = rows[0], rows[1], rows[2:]

@@ -230,6 +230,43 @@ def test_fused_bf16_correction_passes_k128(api, oracle, shape, monkeypatch):
     assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
 
 
+@pytest.mark.parametrize("bn,chunk,corr", [("128", "4", "3"), ("128", "4", "0"), ("256", "4", "3"), ("128", "1", "3"), ("256", "2", "0"), ("128", "3", "3")])
+@pytest.mark.parametrize("shape", [(600, 1300, 256), (1024, 290, 256), (2100, 3000, 250), (420, 2500, 160), (1000, 1057, 192)])
+def test_fused_alternating_chunks(api, oracle, shape, bn, chunk, corr, monkeypatch):
+    """NMF_UMMA_FUSE_ALT=1 (two worker warps per quadrant, K > 128): a warp takes all 32 columns of every other chunk
+    instead of 16 columns of every chunk — same arithmetic per element, so the half-steps must equal the default
+    assignment's bit for bit; shapes with ragged last tiles of 1, 2 and 3 chunks in both directions (a warp with no chunk
+    in a tile still releases it), promotion periods 1-4 (a warp drains a period of P after a chunk it worked on), both S
+    tile widths, with and without the BF16 correction passes, and 30 iterations with cost checks"""
+    monkeypatch.setenv("NMF_UMMA_FUSE_BN", bn)
+    monkeypatch.setenv("NMF_UMMA_CHUNK", chunk)
+    monkeypatch.setenv("NMF_CORR_BF16", corr)
+    W, H, X = rand_problem(*shape, seed=31)
+    def setup(alt, early, prod2, weave):
+        monkeypatch.setenv("NMF_UMMA_FUSE_ALT", alt); monkeypatch.setenv("NMF_UMMA_DRAIN_EARLY", early)
+        monkeypatch.setenv("NMF_UMMA_PROD2", prod2); monkeypatch.setenv("NMF_UMMA_WEAVE", weave)
+    setup("0", "0", "0", "0")
+    H0 = api.dbg_h_step(W, H, X, api.options()); W0 = api.dbg_w_step(W, H, X, api.options())
+    # ... and the other scheduling switches of these kernels, none of which changes a sum or its order: NMF_UMMA_DRAIN_EARLY
+    # (a pending period of P is drained before the wait for the chunk's ring slot instead of after its hand-off),
+    # NMF_UMMA_PROD2 (two TMA producer warps share every stage's loads), NMF_UMMA_WEAVE (the next tile's a-stages sit
+    # between this tile's b-stages in the ring instead of in front of them)
+    for cfg in (("1", "0", "0", "0"), ("0", "1", "0", "0"), ("0", "0", "1", "0"), ("0", "0", "0", "1"), ("1", "1", "1", "1"), ("0", "1", "1", "1")):
+        setup(*cfg)
+        H1 = api.dbg_h_step(W, H, X, api.options()); W1 = api.dbg_w_step(W, H, X, api.options())
+        assert np.array_equal(H1, H0) and np.array_equal(W1, W0), cfg
+    assert max_rel(H1, oracle.h_step(W, H, X, "exact", acc64=True)) < 2e-5
+    assert max_rel(W1, oracle.w_step(W, H, X, "exact", acc64=True)) < 2e-5
+    _, _, _, cost25 = oracle.update_div(W, H, X, 0.0, 25, "exact", acc64=True)
+    Wo, Ho, _, cost = oracle.update_div(W, H, X, 0.0, 30, "exact", acc64=True)
+    Wd, Hd = W.copy(order="F"), H.copy(order="F")
+    res = api.update_div(Wd, Hd, X, 1e-12, 30)
+    assert res.iterations == 30
+    assert max_rel(Wd, Wo) < 1e-4 and max_rel(Hd, Ho) < 1e-4
+    assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
+    assert abs(res.cost - cost25) / cost25 < 1e-5                     # the check at iteration 26: k_fused<H step, COST> with ALT
+
+
 @pytest.mark.parametrize("fuse", ["0", "1"])
 @pytest.mark.parametrize("xs,ws", [(1e-30, 1.0), (1e-20, 1e12), (1e25, 1e-6), (1.0, 1e-18)])
 def test_quotient_extreme_scales(api, oracle, fuse, xs, ws, monkeypatch):
