@@ -24,9 +24,10 @@ struct Tuning {
     int fuse_nw = 0;       // NMF_UMMA_FUSE_NW   worker warps per TMEM quadrant of the fused kernels (0: 4 when Kv <= 128, else 2)
     int fh_defer = 0;      // NMF_UMMA_FH_DEFER  fused H step leaves the update to k_update_h even without a row split
     int corr_bf16 = 3;     // NMF_CORR_BF16      fused kernels: the two correction passes (lo*hi, hi*lo) as BF16 MMAs (bit 0: K = 256, bit 1: K = 128)
-    int weave = 0;         // NMF_UMMA_WEAVE     fused kernels, two S tiles: a- and b-stages interleaved in the ring (even L2 -> SM demand)
+    int weave = -1;        // NMF_UMMA_WEAVE     fused kernels, two S tiles: a- and b-stages interleaved in the ring (even L2 -> SM demand); -1: when K > 128
+                           //                    (measured: C4 -3 %, C5 K=256 -3 %; at K <= 128, quotient in tensor memory, +11 % — off there)
     int prod2 = 0;         // NMF_UMMA_PROD2     fused kernels: warps 0 and 3 share the TMA loads of every ring stage
-    int drain_early = 0;   // NMF_UMMA_DRAIN_EARLY  fused kernels, quotient through shared memory: drain P before the ring-slot wait of a chunk, not after its hand-off
+    int drain_early = 1;   // NMF_UMMA_DRAIN_EARLY  fused kernels, quotient through shared memory: drain P before the ring-slot wait of a chunk, not after its hand-off
     int fuse_alt = 0;      // NMF_UMMA_FUSE_ALT  two worker warps per quadrant (K > 128): a warp takes whole chunks in turn instead of half of every chunk
     int fuse_yt = 1;       // NMF_UMMA_FUSE_YT   K <= 128: stage the quotient in tensor memory (0: in shared memory, as K > 128 does)
     int fuse_bn = 128;     // NMF_UMMA_FUSE_BN   S tile width of the fused kernels (128 double-buffered, or 256)
