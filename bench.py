@@ -243,6 +243,9 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--workload", default=os.environ.get("NMF_BENCH_WORKLOAD", "c4"))
     ap.add_argument("--engine", default="tcgen05")
+    ap.add_argument("--tf32-passes", type=int, default=3, choices=(1, 3),
+                    help="3 = 3xTF32, fp32-equivalent (default, the north star's arithmetic); 1 = single-pass TF32 (~1e-3 accuracy, SURVEY 8(f4)): "
+                         "reported with its own dtype string, never as the headline")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-refcuda", action="store_true")
@@ -283,7 +286,7 @@ def main():
         return float(t.item())
 
     n_off, n_loc = shard(N, rank, world)
-    opt = api.options(engine=args.engine, device=local, restarts=R)
+    opt = api.options(engine=args.engine, device=local, restarts=R, tf32_passes=args.tf32_passes)
     free0 = torch.cuda.mem_get_info()[0]
     sess = api.Session(M, n_loc, K, n_offset=n_off, n_global=N, opt=opt)
     hbm_resident = int(free0 - torch.cuda.mem_get_info()[0])  # the session's device buffers (X, W, H + pairs, partials; no quotient when fused)
@@ -360,7 +363,7 @@ def main():
     # That measurement is itself a power-capped cuBLAS run, so a kernel that moves less through HBM can clock higher and
     # exceed it (frac > 1 is reported as such, never re-based).  The other views are separate keys; `frac_3xtf32` is against
     # the north star's 3xTF32 roofline (bf16 / 6) whatever the kernel executes.
-    units = 2.0 if (corr and fused == 3) else 3.0
+    units = 1.0 if args.tf32_passes == 1 else (2.0 if (corr and fused == 3) else 3.0)
     peak = pk["bf16"] / 2.0 / units
     clk_mhz = (clocks or {}).get("sm_mhz") if rank == 0 else None
     max_mhz = float((clocks or {}).get("sm_max_mhz") or 1965.0)
@@ -404,7 +407,7 @@ def main():
         t0 = time.perf_counter()
         loop_ms = None
         if world == 1 and R == 1:
-            r2 = api.update_div(Wns[0], Hns[0], Xn, 0.0, args.steps, opt=api.options(engine=args.engine, device=local))   # the reference-facing call
+            r2 = api.update_div(Wns[0], Hns[0], Xn, 0.0, args.steps, opt=api.options(engine=args.engine, device=local, tf32_passes=args.tf32_passes))   # the reference-facing call
             loop_ms = r2.device_ms
             call = "update_div(W,H,X,0,steps)"
         elif world == 1:
@@ -437,7 +440,8 @@ def main():
               else "warm L2: the whole working set (X %.1f MB per GPU) is L2-resident across iterations, as it is in a real run of this size" % (xbytes / 1e6))
         line = {"metric": "nmf_iterations_per_s", "value": value, "unit": "iterations/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-                "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f32 (3xTF32 tensor-core products" + (", correction passes as BF16 MMAs" if corr else "") + ", fp32 accumulate)",
+                "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": ("tf32 (single-pass TF32 products, fp32 accumulate: reduced precision, NOT the headline arithmetic)" if args.tf32_passes == 1 else
+                          "f32 (3xTF32 tensor-core products" + (", correction passes as BF16 MMAs" if corr else "") + ", fp32 accumulate)"),
                 "data": "synthetic",
                 "config": {"workload": desc, "M": M, "N": N, "K": K, "restarts": R, "columns_per_gpu": n_loc,
                            "parallelism": f"column-sharded x{world}", "engine": args.engine,

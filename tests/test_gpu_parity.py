@@ -554,3 +554,22 @@ def test_shape_mismatch_raises(api):
     W, H, X = rand_problem(64, 64, 32, seed=1)
     with pytest.raises(api.NmfError):
         api.update_div(W, H[:, :10].copy(order="F"), X, 0.0, 1)
+
+
+@pytest.mark.parametrize("shape", [(600, 1300, 256), (513, 3000, 40)])
+def test_single_pass_tf32_measured_accuracy(api, oracle, shape):
+    """the reduced-precision mode (nmf_options.tf32_passes = 1 / NMF_TF32_PASSES=1: one TF32 MMA per product
+    instead of three) with its accuracy MEASURED — a half step lands at 1e-4..3e-3 of the fp64 oracle (TF32 keeps 11 bits),
+    30 iterations stay within 1e-2 and the divergence within 1e-3; the default three-pass arithmetic on the same inputs is
+    two orders of magnitude closer.  It is a user's choice, never the default and never a bench headline."""
+    W, H, X = rand_problem(*shape, seed=41)
+    Ho = oracle.h_step(W, H, X, "exact", acc64=True)
+    e3 = max_rel(api.dbg_h_step(W, H, X, api.options()), Ho)
+    e1 = max_rel(api.dbg_h_step(W, H, X, api.options(tf32_passes=1)), Ho)
+    assert e3 < 2e-5 and 1e-5 < e1 < 3e-3 and e1 > 10 * e3, (e1, e3)
+    Wo, Ho30, _, cost = oracle.update_div(W, H, X, 0.0, 30, "exact", acc64=True)
+    Wd, Hd = W.copy(order="F"), H.copy(order="F")
+    api.update_div(Wd, Hd, X, 0.0, 30, opt=api.options(tf32_passes=1))
+    eW, eH = max_rel(Wd, Wo), max_rel(Hd, Ho30)
+    assert eW < 1e-2 and eH < 1e-2 and abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-3, (eW, eH)
+    print(f"single-pass TF32 {shape}: half step {e1:.2e} (3xTF32 {e3:.2e}), 30 iterations W {eW:.2e} H {eH:.2e}")
