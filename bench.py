@@ -363,7 +363,7 @@ def main():
     # That measurement is itself a power-capped cuBLAS run, so a kernel that moves less through HBM can clock higher and
     # exceed it (frac > 1 is reported as such, never re-based).  The other views are separate keys; `frac_3xtf32` is against
     # the north star's 3xTF32 roofline (bf16 / 6) whatever the kernel executes.
-    units = 1.0 if args.tf32_passes == 1 else (2.0 if (corr and fused == 3) else 3.0)
+    units = 1.0 if args.tf32_passes == 1 else (2.0 if corr else 3.0)
     peak = pk["bf16"] / 2.0 / units
     clk_mhz = (clocks or {}).get("sm_mhz") if rank == 0 else None
     max_mhz = float((clocks or {}).get("sm_max_mhz") or 1965.0)

@@ -132,7 +132,7 @@ nmf_session_impl* session_create(int M, int n_local, int K, long long n_offset, 
             if (!umma::fused_both_wanted(d, opt.tf32_passes, tn) || (tn.keep_quotient && R == 1)) s->Y = dalloc<float>(d.szXa());
             s->Whi = dalloc<float>(d.szW()); s->Wlo = dalloc<float>(d.szW());
             s->Hhi = dalloc<float>(d.szHa()); s->Hlo = dalloc<float>(d.szHa());
-            if (umma::corr_bf16_wanted(d, opt.tf32_passes, tn)) {
+            if (umma::corr_bf16_wanted(d, opt.tf32_passes, tn) || umma::corr_bf16_wanted_2k(d, opt.tf32_passes, tn)) {
                 s->Wbf = dalloc<unsigned short>(d.szW()); s->Wlb = dalloc<unsigned short>(d.szW());
                 s->Hbf = dalloc<unsigned short>(d.szHa()); s->Hlb = dalloc<unsigned short>(d.szHa());
                 CUDA_CHECK(cudaMemsetAsync(s->Hbf, 0, d.szHa() * 2, s->stream));      // the padding columns stay zero

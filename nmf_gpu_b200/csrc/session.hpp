@@ -23,7 +23,8 @@ struct Tuning {
     int fhsplit = 0;       // NMF_UMMA_FHSPLIT   forced row-split count of the fused H step (0: the cost model chooses)
     int fuse_nw = 0;       // NMF_UMMA_FUSE_NW   worker warps per TMEM quadrant of the fused kernels (0: 4 when Kv <= 128, else 2)
     int fh_defer = 0;      // NMF_UMMA_FH_DEFER  fused H step leaves the update to k_update_h even without a row split
-    int corr_bf16 = 3;     // NMF_CORR_BF16      fused kernels: the two correction passes (lo*hi, hi*lo) as BF16 MMAs (bit 0: K = 256, bit 1: K = 128)
+    int corr_bf16 = 7;     // NMF_CORR_BF16      the two correction passes (lo*hi, hi*lo) as BF16 MMAs: fused kernels (bit 0: K = 256, bit 1: K = 128),
+                           //                    two-kernel path of sessions without fused half-iterations (bit 2: K > 256)
     int weave = -1;        // NMF_UMMA_WEAVE     fused kernels, two S tiles: a- and b-stages interleaved in the ring (even L2 -> SM demand); -1: when K > 128
                            //                    (measured: C4 -3 %, C5 K=256 -3 %; at K <= 128, quotient in tensor memory, +11 % — off there)
     int prod2 = 0;         // NMF_UMMA_PROD2     fused kernels: warps 0 and 3 share the TMA loads of every ring stage
@@ -141,6 +142,7 @@ int   fused_cost_partial_count(const Dims& d, int passes, const Tuning& tn);   /
 bool  fused_both_wanted(const Dims& d, int passes, const Tuning& tn);
 bool  fused_shape_ok(int Kr, int passes, const Tuning& tn);   // Kr (one restart's padded K) is a multiple of 64 and <= 256
 unsigned int protocol_error(const nmf_session_impl& s);
+bool  corr_bf16_wanted_2k(const Dims& d, int passes, const Tuning& tn);   // ... its two-kernel path does (K > 256)
 bool  corr_bf16_wanted(const Dims& d, int passes, const Tuning& tn);   // the session's fused kernels run their correction passes in BF16
 bool  fused_h_needs_part(const Dims& d, int passes, const Tuning& tn);   // the fused H step writes partial sums (row split or deferred update)
 // raw contraction for descriptor bring-up (nmf_dbg_gemm)

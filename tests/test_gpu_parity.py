@@ -230,6 +230,32 @@ def test_fused_bf16_correction_passes_k128(api, oracle, shape, monkeypatch):
     assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5
 
 
+@pytest.mark.parametrize("shape", [(1024, 1300, 512), (600, 2100, 384), (2049, 700, 512), (300, 5000, 640)])
+def test_two_kernel_bf16_correction_passes(api, oracle, shape, monkeypatch):
+    """K > 256 (no fused half-iterations: k_umma quotient kernel + the two GEMMs that consume the quotient) with the
+    correction passes as BF16 MMAs (NMF_CORR_BF16 bit 2): pre-split operands arrive as hi + bf + lb tiles by
+    TMA, the raw quotient is split into hi / bf / lb by the splitter warps (K-major tiles in the H update, MN-major in
+    the W numerator).  Half-steps against the oracle and against the three-TF32-pass kernels, 30 iterations with a cost
+    check."""
+    W, H, X = rand_problem(*shape, seed=37)
+    monkeypatch.setenv("NMF_CORR_BF16", "3")
+    H0 = api.dbg_h_step(W, H, X, api.options()); W0 = api.dbg_w_step(W, H, X, api.options())
+    monkeypatch.setenv("NMF_CORR_BF16", "7")
+    with api.Session(*shape) as s:
+        assert s.fused_steps() == 0 and s.corr_bf16()
+    H1 = api.dbg_h_step(W, H, X, api.options())
+    assert max_rel(H1, oracle.h_step(W, H, X, "exact", acc64=True)) < 2e-5 and max_rel(H1, H0) < 1e-5
+    W1 = api.dbg_w_step(W, H, X, api.options())
+    assert max_rel(W1, oracle.w_step(W, H, X, "exact", acc64=True)) < 2e-5 and max_rel(W1, W0) < 1e-5
+    _, _, _, cost25 = oracle.update_div(W, H, X, 0.0, 25, "exact", acc64=True)
+    Wo, Ho, _, cost = oracle.update_div(W, H, X, 0.0, 30, "exact", acc64=True)
+    Wd, Hd = W.copy(order="F"), H.copy(order="F")
+    res = api.update_div(Wd, Hd, X, 1e-12, 30)
+    assert res.iterations == 30
+    assert max_rel(Wd, Wo) < 1e-4 and max_rel(Hd, Ho) < 1e-4
+    assert abs(oracle.kl(Wd, Hd, X) - cost) / cost < 1e-5 and abs(res.cost - cost25) / cost25 < 1e-5
+
+
 @pytest.mark.parametrize("bn,chunk,corr", [("128", "4", "3"), ("128", "4", "0"), ("256", "4", "3"), ("128", "1", "3"), ("256", "2", "0"), ("128", "3", "3")])
 @pytest.mark.parametrize("shape", [(600, 1300, 256), (1024, 290, 256), (2100, 3000, 250), (420, 2500, 160), (1000, 1057, 192)])
 def test_fused_alternating_chunks(api, oracle, shape, bn, chunk, corr, monkeypatch):
