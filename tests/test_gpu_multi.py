@@ -45,7 +45,7 @@ def test_torchrun_sharded_vs_single_gpu_and_oracle(two_gpus, fuse):
     assert p["world"] == 2 and p["exact"]["W_vs_oracle"] < 1e-4 and p["exact"]["H_vs_oracle"] < 1e-4
 
 
-@pytest.mark.parametrize("K,verbose", [(128, 0), (128, 1), (320, 1)])
+@pytest.mark.parametrize("K,verbose", [(128, 0), (128, 1), (320, 1), (512, 0)])
 def test_update_div_num_gpus_2(two_gpus, K, verbose):
     """README-style call on 2 GPUs from one process; verbose = 1 used to leave rank 0 alone in the cost allreduce"""
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "multi_gpu_update_div.py"), "2", str(K), str(verbose)],
