@@ -428,6 +428,21 @@ def main():
                "seconds": dt, "call": call, "loop_device_ms": loop_ms,
                "outside_loop_seconds": (dt - loop_ms * 1e-3) if loop_ms else None,      # allocation + H2D + D2H (+ graph capture)
                "host_cpus_near_gpu": len(near_cpus) if near_cpus else None}
+        # the box's own pinned-memory H2D rate, measured right here (1 GiB, best of 3): the call above is PCIe-bound, and the
+        # boxes of the pool differ (52-54 GB/s on most, 12 GB/s seen on one) — this says which kind the line came from
+        try:
+            probe = Xh.view(-1)[: min(Xh.numel(), 1 << 28)]
+            dst = torch.empty(probe.numel(), dtype=torch.float32, device=f"cuda:{local}")
+            best = None
+            for _ in range(3):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); dst.copy_(probe, non_blocking=True); e1.record(); e1.synchronize()
+                ms = e0.elapsed_time(e1); best = ms if best is None else min(best, ms)
+            e2e["h2d_probe_GBps"] = probe.numel() * 4 / (best * 1e-3) / 1e9
+            e2e["h2d_call_GBps"] = (4.0 * M * n_loc / e2e["outside_loop_seconds"] / 1e9) if e2e.get("outside_loop_seconds") else None
+            del dst
+        except Exception as ex:                                   # a probe must never cost the line
+            e2e["h2d_probe_GBps"] = None; e2e["h2d_probe_error"] = str(ex)[:100]
         del Xh, Whs, Hhs
     parity = None
     if world > 1:
