@@ -191,9 +191,10 @@ int nmf_session_cost(nmf_session *s, double *cost);
  * way.  A session with both bits set allocates no M x N quotient buffer. */
 int nmf_session_fused_steps(const nmf_session *s);
 
-/* 1 when this session's fused kernels run the two correction passes of every 3xTF32 product (lo*hi, hi*lo) as BF16
+/* 1 when this session's tensor-core kernels run the two correction passes of every 3xTF32 product (lo*hi, hi*lo) as BF16
  * MMAs on bf16(x) / bf16(x - tf32(x)) operands — 8 instead of 12 tensor-pipe time units per 32-deep block, ~2^-20
- * relative error per product; default at a padded K of 256 (NMF_CORR_BF16=0: never, =3: at K = 128 too).
+ * relative error per product.  Default (NMF_CORR_BF16=7): the fused kernels at a padded K of 256 (bit 0)
+ * and 128 (bit 1), the two-kernel path at K > 256, a multiple of 128 (bit 2); NMF_CORR_BF16=0: never.
  * Informational, like nmf_session_fused_steps: results stay within the same tolerances. */
 int nmf_session_corr_bf16(const nmf_session *s);
 
